@@ -1,0 +1,409 @@
+// TEST INFRASTRUCTURE — the CPU oracle's env layer and C ABI (see oracle/README.md). PARITY UNPINNED.
+//
+// Restates reset / step / wait_until_stable / reward / termination / observation of the five in-scope envs:
+//   BallBalance      /root/reference/urgym/envs/env_ball_balance_v0.py:94-170
+//   TwoBallsBalance  /root/reference/urgym/envs/env_two_balls_balance_v0.py:95-233
+//   CubesPush        /root/reference/urgym/envs/env_cubes_push_v0.py:104-246
+//   CubesGrasp       /root/reference/urgym/envs/env_cubes_grasp_v0.py:100-327
+//   Golf             /root/reference/urgym/envs/env_golf_v0.py:104-358
+// and the robot helper /root/reference/urgym/base/robot.py:85-128,213-218. Episode limits from
+// /root/reference/urgym/envs/__init__.py:10-44 (the TimeLimit wrapper's `truncated`).
+//
+// Only tests/, __graft_entry__.smoke() and bench.py's cpu_baseline / --impl reference legs may load this library.
+#include <cstdio>
+
+#include "urgo_engine.h"
+
+namespace urgo {
+
+static const double REST_POSE[6] = {-1.5690622952052096, -1.5446774605904932, 1.343946009733127,
+                                    -1.3708613585093699, -1.5707970583733368, 0.0009377758247187636};  // robot.py:182-183
+static const double PI = 3.14159265358979323846;
+
+inline uint64_t splitmix(uint64_t x) {
+  x += 0x9E3779B97F4A7C15ull; x = (x ^ (x >> 30)) * 0xBF58476D1CE4E5B9ull; x = (x ^ (x >> 27)) * 0x94D049BB133111EBull;
+  return x ^ (x >> 31);
+}
+// Counter-based uniform in [0,1) with 24 bits, so fp32 and fp64 consumers see the same variate.
+inline double urand(uint64_t seed, uint32_t env, uint32_t episode, uint32_t draw) {
+  uint64_t h = splitmix(seed ^ splitmix(((uint64_t)env << 32) | episode) ^ splitmix(0xD1B54A32D192ED03ull * (uint64_t)(draw + 1)));
+  return (double)(h >> 40) * (1.0 / 16777216.0);
+}
+inline double gripper_angle(double open_length) { return 0.715 - std::asin((open_length - 0.010) / 0.1143); }  // robot.py:215
+// utilities.py:192-207
+inline double geometric_distance_reward(double value, double ts, double tmax) {
+  value = std::fmax(value, 1e-10);
+  double f1 = (value - ts) / value, f2 = std::fmax(tmax - value, 1e-10);
+  return -std::tanh(f1 / f2);
+}
+
+struct Env {
+  World w;
+  int env_type; uint64_t seed; uint32_t gidx;
+  int step_count = 0; uint32_t episode = 0;
+  bool approached = false, grasped = false;
+  Q4 vertical;
+  bool sparse = false;
+  int last_contacts[MAXC][2]; int last_ncontacts = 0;
+  long total_ticks = 0;
+
+  Env(int t, uint64_t s, uint32_t g) : w(t), env_type(t), seed(s), gidx(g) {}
+
+  int settle() {  // wait_until_stable, e.g. env_ball_balance_v0.py:94-103
+    double prev[NDOF]; std::memcpy(prev, w.rob.q, sizeof(prev));
+    int n = 0;
+    for (; n < BP_SETTLE_MAX_TICKS;) {
+      w.tick(); n++;
+      double s = 0; for (int d = 0; d < NDOF; d++) s += std::fabs(prev[d] - w.rob.q[d]);
+      if (s < BP_SETTLE_THRESHOLD) break;
+      std::memcpy(prev, w.rob.q, sizeof(prev));
+    }
+    total_ticks += n;
+    return n;
+  }
+  void move_ee_end(V3 pos, Q4 q) { double t[6]; w.ik(pos, q, t); for (int i = 0; i < 6; i++) w.target[i] = t[i]; w.arm_armed = true; }
+  void move_gripper(double len) { w.target[6] = gripper_angle(len); w.grip_armed = true; }
+  void ee_pose(V3& p, Q4& q) { w.rob.fk(); p = w.rob.p[7]; q = w.rob.quat[7]; }
+  void spawn(int b, V3 pos, Q4 q) { FreeBody& B = w.fb[b]; B.pos = pos; B.quat = q; B.lin = V3(); B.ang = V3(); B.active = true; }
+  double draw(const double* ov, int k) { return ov ? ov[k] : urand(seed, gidx, episode, (uint32_t)k); }
+
+  bool touch(bool (*pred)(const ShapeDef&, const ShapeDef&, void*), void* ctx = nullptr) const {
+    for (auto& c : w.contacts) if (pred(w.sc.shapes[c.sa], w.sc.shapes[c.sb], ctx)) return true;
+    return false;
+  }
+  double opening() {  // env_cubes_grasp_v0.py:340-377
+    w.rob.fk();
+    double v = norm(w.rob.p[16] - w.rob.p[11]) - 0.052;
+    v = std::fmax(0.0, std::fmin(0.085, v));
+    return v / 0.085;
+  }
+  V3 club_foot() const { return w.fb[0].pos + quat_to_mat(w.fb[0].quat) * V3(0, 0, -0.09 - CLUB_ZC); }  // env_golf_v0.py:368-373
+
+  int reset(const double* ov, double* obs) {
+    episode++; step_count = 0; approached = grasped = false;
+    int ticks = 0;
+    for (int b = 0; b < MAXFREE; b++) w.fb[b].active = false;
+    for (int i = 0; i < 6; i++) { w.rob.q[i] = REST_POSE[i]; w.rob.qd[i] = 0; }   // robot.py:93-94
+    for (int i = 0; i < BP_RESET_ARM_TICKS; i++) { w.tick(); ticks++; total_ticks++; }  // robot.py:97-98
+    move_gripper(0.085);                                                            // robot.py:100-101
+    V3 ep; Q4 eq;
+    switch (env_type) {
+      case ENV_BALL: case ENV_TWO: {
+        move_ee_end(V3(0.0, -0.60, 0.60), Q4(0.50, -0.50, -0.50, 0.50));
+        move_gripper(0.085 * 0.2);
+        ticks += settle();
+        ee_pose(ep, eq);
+        V3 gc = w.gripper_center();
+        V3 pp(ep.x, ep.y - 0.2, gc.z);
+        spawn(0, pp, Q4());
+        if (env_type == ENV_BALL) {
+          spawn(1, pp + V3(-0.03 + 0.06 * draw(ov, 0), -0.08 + 0.10 * draw(ov, 1), 0.2 + 0.02), Q4());
+        } else {
+          double r = 0.003;
+          spawn(1, pp + V3(-0.03 + 0.06 * draw(ov, 0), -0.08 + 0.035 * draw(ov, 1), 0.2 + r), Q4());
+          spawn(2, pp + V3(-0.03 + 0.06 * draw(ov, 2), -0.015 + 0.035 * draw(ov, 3), 0.2 - r), Q4());
+        }
+        move_gripper(0.0);
+        ticks += settle();
+        break;
+      }
+      case ENV_PUSH: {
+        spawn(0, V3(0.0, -0.5, 0.1), Q4());
+        V3 c1(-0.1 + 0.2 * draw(ov, 0), -0.7, 0.1);
+        spawn(1, c1, Q4());
+        vertical = Q4() * axis_angle(V3(0, 1, 0), PI / 2);  // utilities.py:134-149
+        move_ee_end(c1 + V3(0, 0, 0.2), vertical);
+        move_gripper(0.0);
+        ticks += settle();
+        break;
+      }
+      case ENV_GRASP: {
+        double r = 0.5 + 0.3 * draw(ov, 0), th = -PI + PI * draw(ov, 1);
+        spawn(0, V3(r * std::cos(th), r * std::sin(th), 0.1), Q4());
+        ee_pose(ep, eq);
+        move_ee_end(ep, eq);
+        ticks += settle();
+        break;
+      }
+      case ENV_GOLF: {
+        vertical = Q4(0.0, 0.0, -0.70, 0.70);
+        move_ee_end(V3(0.0, -0.60, 0.40), vertical);
+        move_gripper(0.085 * 0.2);
+        ticks += settle();
+        V3 gc = w.gripper_center();
+        spawn(0, gc + V3(0, 0, -0.05 + CLUB_ZC), Q4());
+        spawn(1, V3(0.0 + (-0.2 + 0.4 * draw(ov, 0)), -0.7 + (-0.1 + 0.2 * draw(ov, 1)), 0.1), Q4());
+        move_gripper(0.0);
+        ticks += settle();
+        break;
+      }
+    }
+    observe(obs);
+    return ticks;
+  }
+
+  void observe(double* o) {
+    V3 ep; Q4 eq;
+    switch (env_type) {
+      case ENV_BALL: case ENV_TWO: {
+        V3 e = euler_from_quat(w.fb[0].quat);
+        o[0] = e.x; o[1] = e.y; o[2] = e.z;
+        for (int b = 1; b < w.sc.nfree; b++) { V3 d = w.fb[0].pos - w.fb[b].pos; o[3 * b] = d.x; o[3 * b + 1] = d.y; o[3 * b + 2] = d.z; }
+        break;
+      }
+      case ENV_PUSH:
+        ee_pose(ep, eq);
+        o[0] = ep.x; o[1] = ep.y; o[2] = ep.z;
+        for (int b = 0; b < 2; b++) { o[3 + 3 * b] = w.fb[b].pos.x; o[4 + 3 * b] = w.fb[b].pos.y; o[5 + 3 * b] = w.fb[b].pos.z; }
+        break;
+      case ENV_GRASP:
+        ee_pose(ep, eq);
+        o[0] = approached; o[1] = grasped;
+        o[2] = ep.x; o[3] = ep.y; o[4] = ep.z; o[5] = eq.x; o[6] = eq.y; o[7] = eq.z; o[8] = eq.w;
+        o[9] = opening();
+        o[10] = w.fb[0].pos.x; o[11] = w.fb[0].pos.y; o[12] = w.fb[0].pos.z;
+        o[13] = w.fb[0].quat.x; o[14] = w.fb[0].quat.y; o[15] = w.fb[0].quat.z; o[16] = w.fb[0].quat.w;
+        break;
+      case ENV_GOLF: {
+        V3 s = club_foot(), b = w.fb[1].pos, h(0, -0.6, 0.02);
+        o[0] = s.x; o[1] = s.y; o[2] = s.z;
+        V3 d1 = s - b, d2 = h - b;
+        o[3] = d1.x; o[4] = d1.y; o[5] = d1.z; o[6] = d2.x; o[7] = d2.y; o[8] = d2.z;
+        break;
+      }
+    }
+  }
+
+  // One gym step without auto-reset. Returns settle ticks.
+  int step(const double* a, double u, double* obs, double* reward, uint8_t* terminated, uint8_t* truncated, uint8_t* success) {
+    V3 ep; Q4 eq;
+    double rew = 0; bool term = false, succ = false;
+    int n = 0;
+    switch (env_type) {
+      case ENV_BALL: case ENV_TWO: {
+        if (env_type == ENV_TWO) for (int i = 0; i < 3; i++) rew -= std::fabs(a[i]);
+        ee_pose(ep, eq);
+        V3 e = euler_from_quat(eq);
+        move_ee_end(ep, quat_from_euler(e.x + a[0], e.y + a[1], e.z + a[2]));
+        n = settle();
+        rew += 1;
+        if (env_type == ENV_BALL) {
+          term = w.fb[1].pos.z < w.fb[0].pos.z;
+        } else {
+          for (int b = 1; b <= 2; b++) for (int k = 0; k < 2; k++) { double x = std::fabs(w.fb[b].pos[k]); rew += x > 1 ? 0.0 : 1 - x * x; }
+          term = w.fb[1].pos.z < w.fb[0].pos.z || w.fb[2].pos.z < w.fb[0].pos.z;
+        }
+        break;
+      }
+      case ENV_PUSH: {
+        ee_pose(ep, eq);
+        move_ee_end(ep + V3(a[0], a[1], a[2]), vertical);
+        n = settle();
+        bool table = touch([](const ShapeDef& A, const ShapeDef& B, void*) { return A.body == 0 && B.body < 0 && A.link != 0; });
+        bool fingers = touch([](const ShapeDef& A, const ShapeDef& B, void*) { return A.body == 0 && B.body == 2 && A.link >= 9 && A.link <= 18; });
+        if (table) { rew -= 0.01; }
+        else if (fingers) {
+          double d = norm(w.fb[0].pos - w.fb[1].pos);
+          rew = 0;
+          if (!sparse) rew += geometric_distance_reward(d, 0.1, 0.5) / 10;
+          if (d < 0.05) { rew += 10; succ = true; }
+          rew += 0.1; term = succ;
+        }
+        rew -= 0.1;
+        break;
+      }
+      case ENV_GRASP: {
+        double a0 = a[0], a1 = a[1];
+        int sel = (a0 + a1 == 0) ? (u < 0.5 ? 0 : 1) : (u * (a0 + a1) < a0 ? 0 : 1);
+        if (sel == 0) { for (int i = 0; i < 6; i++) w.target[i] = a[2 + i]; w.arm_armed = true; }
+        else move_gripper(a[8] < 0.5 ? 0.085 : 0.0);
+        n = settle();
+        V3 gc = w.gripper_center();
+        double d = norm(gc - w.fb[0].pos);
+        bool l = touch([](const ShapeDef& A, const ShapeDef& B, void*) { return A.body == 0 && B.body == 1 && A.link >= 11 && A.link <= 13; });
+        bool r = touch([](const ShapeDef& A, const ShapeDef& B, void*) { return A.body == 0 && B.body == 1 && A.link >= 16 && A.link <= 18; });
+        bool grasp_now = l && r;
+        if (!approached) {
+          rew += geometric_distance_reward(d, 0.5, 2) / 4;
+          if (d < 0.05 && opening() > 0.50) { approached = true; rew += 5; }
+        } else if (!grasped) {
+          if (grasp_now) { grasped = true; rew += 5; }
+        } else {
+          if (grasp_now && w.fb[0].pos.z > 0.2) { rew += 10; term = true; succ = true; }
+        }
+        rew -= 0.1;
+        break;
+      }
+      case ENV_GOLF: {
+        ee_pose(ep, eq);
+        move_ee_end(ep + V3(a[0], a[1], a[2]), vertical);
+        n = settle();
+        V3 hole(0, -0.6, 0.02), ball = w.fb[1].pos;
+        bool in_fingers = touch([](const ShapeDef& A, const ShapeDef& B, void*) { return A.body == 0 && B.body == 1 && A.link >= 9 && A.link <= 18; });
+        if (norm(hole - ball) < 0.05) { rew += 10; succ = true; term = true; }
+        else if (!in_fingers) { rew -= 5; term = true; }
+        else if (ball.z < 0) { rew -= 10; term = true; }
+        else {
+          bool floor_hit = touch([](const ShapeDef& A, const ShapeDef& B, void*) { return (A.body == 0 || A.body == 1) && B.body < 0 && B.link == 1; });
+          if (floor_hit) rew -= 0.01;
+          if (!sparse) rew += geometric_distance_reward(norm(club_foot() - ball), 0.1, 0.5) / 10;
+          bool hit = touch([](const ShapeDef& A, const ShapeDef& B, void*) { return A.body == 1 && B.body == 2; });
+          if (hit) { rew += 0.1; if (!sparse) rew += geometric_distance_reward(norm(hole - ball), 0.1, 0.5) / 10; }
+        }
+        rew -= 0.1;
+        break;
+      }
+    }
+    last_ncontacts = (int)w.contacts.size();
+    for (int i = 0; i < last_ncontacts; i++) { last_contacts[i][0] = w.contacts[i].sa; last_contacts[i][1] = w.contacts[i].sb; }
+    step_count++;
+    *reward = rew; *terminated = term; *success = succ; *truncated = step_count >= w.sc.max_steps;
+    observe(obs);
+    return n;
+  }
+
+  void get_state(double* s) const {
+    std::memset(s, 0, sizeof(double) * STATE_SLOTS);
+    for (int d = 0; d < NDOF; d++) { s[d] = w.rob.q[d]; s[12 + d] = w.rob.qd[d]; }
+    for (int m = 0; m < NMOTOR; m++) s[24 + m] = w.target[m];
+    int flags = (w.arm_armed ? 1 : 0) | (w.grip_armed ? 2 : 0) | (approached ? 4 : 0) | (grasped ? 8 : 0);
+    for (int b = 0; b < MAXFREE; b++) if (w.fb[b].active) flags |= 16 << b;
+    s[31] = flags; s[32] = step_count; s[33] = episode;
+    s[34] = vertical.x; s[35] = vertical.y; s[36] = vertical.z; s[37] = vertical.w;
+    for (int b = 0; b < MAXFREE; b++) {
+      const FreeBody& B = w.fb[b]; double* p = s + 38 + 13 * b;
+      p[0] = B.pos.x; p[1] = B.pos.y; p[2] = B.pos.z; p[3] = B.quat.x; p[4] = B.quat.y; p[5] = B.quat.z; p[6] = B.quat.w;
+      p[7] = B.lin.x; p[8] = B.lin.y; p[9] = B.lin.z; p[10] = B.ang.x; p[11] = B.ang.y; p[12] = B.ang.z;
+    }
+  }
+  void set_state(const double* s) {
+    for (int d = 0; d < NDOF; d++) { w.rob.q[d] = s[d]; w.rob.qd[d] = s[12 + d]; }
+    for (int m = 0; m < NMOTOR; m++) w.target[m] = s[24 + m];
+    int flags = (int)s[31];
+    w.arm_armed = flags & 1; w.grip_armed = flags & 2; approached = flags & 4; grasped = flags & 8;
+    step_count = (int)s[32]; episode = (uint32_t)s[33];
+    vertical = Q4(s[34], s[35], s[36], s[37]);
+    for (int b = 0; b < MAXFREE; b++) {
+      FreeBody& B = w.fb[b]; const double* p = s + 38 + 13 * b;
+      B.active = (flags >> (4 + b)) & 1;
+      B.pos = V3(p[0], p[1], p[2]); B.quat = Q4(p[3], p[4], p[5], p[6]); B.lin = V3(p[7], p[8], p[9]); B.ang = V3(p[10], p[11], p[12]);
+    }
+  }
+};
+
+struct Batch { std::vector<Env> envs; int env_type; };
+
+}  // namespace urgo
+
+using namespace urgo;
+
+extern "C" {
+
+void* urgo_create(int env_type, int num_envs, uint64_t seed, int env_index_offset) {
+  if (env_type < 0 || env_type > 4 || num_envs <= 0) return nullptr;
+  Batch* b = new Batch; b->env_type = env_type;
+  b->envs.reserve(num_envs);
+  for (int i = 0; i < num_envs; i++) b->envs.emplace_back(env_type, seed, (uint32_t)(env_index_offset + i));
+  return b;
+}
+void urgo_destroy(void* h) { delete (Batch*)h; }
+int urgo_obs_dim(int t) { return make_scene(t).obs_dim; }
+int urgo_act_dim(int t) { return make_scene(t).act_dim; }
+int urgo_max_steps(int t) { return make_scene(t).max_steps; }
+int urgo_num_shapes(int t) { return (int)make_scene(t).shapes.size(); }
+// shape descriptor: body, link
+void urgo_shape_info(int t, int idx, int* body, int* link) { Scene s = make_scene(t); *body = s.shapes[idx].body; *link = s.shapes[idx].link; }
+void urgo_set_sparse(void* h, int sparse) { for (auto& e : ((Batch*)h)->envs) e.sparse = sparse != 0; }
+
+// env range [lo, hi) so that callers can spread envs over host threads (envs are independent)
+int urgo_reset_range(void* h, int lo, int hi, const uint8_t* mask, const double* draws, double* obs, int32_t* nticks) {
+  Batch* b = (Batch*)h; int od = make_scene(b->env_type).obs_dim;
+  for (int i = lo; i < hi; i++) {
+    if (mask && !mask[i]) continue;
+    int n = b->envs[i].reset(draws ? draws + 4 * i : nullptr, obs + (size_t)od * i);
+    if (nticks) nticks[i] = n;
+  }
+  return 0;
+}
+int urgo_reset(void* h, const uint8_t* mask, const double* draws, double* obs, int32_t* nticks) {
+  return urgo_reset_range(h, 0, (int)((Batch*)h)->envs.size(), mask, draws, obs, nticks);
+}
+int urgo_step_range(void* h, int lo, int hi, const double* action, const double* u, const double* draws, double* obs, double* reward,
+                    uint8_t* terminated, uint8_t* truncated, uint8_t* success, double* final_obs, int32_t* nticks, int autoreset) {
+  Batch* b = (Batch*)h; Scene sc = make_scene(b->env_type); int od = sc.obs_dim, ad = sc.act_dim;
+  for (int i = lo; i < hi; i++) {
+    Env& e = b->envs[i];
+    double uu = u ? u[i] : urand(e.seed, e.gidx, e.episode, 16u + (uint32_t)e.step_count);
+    int n = e.step(action + (size_t)ad * i, uu, obs + (size_t)od * i, reward + i, terminated + i, truncated + i, success + i);
+    int nr = 0;
+    if (final_obs) std::memcpy(final_obs + (size_t)od * i, obs + (size_t)od * i, sizeof(double) * od);
+    if (autoreset && (terminated[i] || truncated[i])) nr = e.reset(draws ? draws + 4 * i : nullptr, obs + (size_t)od * i);
+    if (nticks) { nticks[2 * i] = n; nticks[2 * i + 1] = nr; }
+  }
+  return 0;
+}
+int urgo_step(void* h, const double* action, const double* u, const double* draws, double* obs, double* reward, uint8_t* terminated,
+              uint8_t* truncated, uint8_t* success, double* final_obs, int32_t* nticks, int autoreset) {
+  return urgo_step_range(h, 0, (int)((Batch*)h)->envs.size(), action, u, draws, obs, reward, terminated, truncated, success, final_obs, nticks, autoreset);
+}
+int urgo_get_state(void* h, double* out) { Batch* b = (Batch*)h; for (size_t i = 0; i < b->envs.size(); i++) b->envs[i].get_state(out + STATE_SLOTS * i); return 0; }
+int urgo_set_state(void* h, const double* in) { Batch* b = (Batch*)h; for (size_t i = 0; i < b->envs.size(); i++) b->envs[i].set_state(in + STATE_SLOTS * i); return 0; }
+int urgo_contacts(void* h, int32_t* pairs, int32_t* count) {
+  Batch* b = (Batch*)h;
+  for (size_t i = 0; i < b->envs.size(); i++) {
+    const Env& e = b->envs[i]; count[i] = e.last_ncontacts;
+    for (int k = 0; k < MAXC; k++) { pairs[(i * MAXC + k) * 2] = k < e.last_ncontacts ? e.last_contacts[k][0] : -1; pairs[(i * MAXC + k) * 2 + 1] = k < e.last_ncontacts ? e.last_contacts[k][1] : -1; }
+  }
+  return 0;
+}
+long urgo_total_ticks(void* h) { long s = 0; for (auto& e : ((Batch*)h)->envs) s += e.total_ticks; return s; }
+
+// ---- unit-level entry points for parity tests
+// n ticks of raw physics on every env (no env logic); detail outputs of the last tick are optional
+int urgo_tick(void* h, int nticks) { for (auto& e : ((Batch*)h)->envs) for (int k = 0; k < nticks; k++) e.w.tick(); return 0; }
+int urgo_last_contacts_detail(void* h, int env, double* out /*[MAXC][11]: sa, sb, posB3, n3, dist, mu, roll*/) {
+  Env& e = ((Batch*)h)->envs[env]; int n = (int)e.w.contacts.size();
+  for (int i = 0; i < n; i++) {
+    const Contact& c = e.w.contacts[i]; double* o = out + 11 * i;
+    o[0] = c.sa; o[1] = c.sb; o[2] = c.posB.x; o[3] = c.posB.y; o[4] = c.posB.z; o[5] = c.n.x; o[6] = c.n.y; o[7] = c.n.z; o[8] = c.dist; o[9] = c.mu; o[10] = c.roll;
+  }
+  return n;
+}
+int urgo_last_iters(void* h, int env) { return ((Batch*)h)->envs[env].w.last_iters; }
+// link frames for joint vector q[12]: out[19][7] = pos xyz, quat xyzw (getLinkState(...)[4], [5])
+void urgo_fk(const double* q, double* out) {
+  Robot r; std::memcpy(r.q, q, sizeof(double) * NDOF); r.fk();
+  for (int i = 0; i < URG_NLINK; i++) { double* o = out + 7 * i; o[0] = r.p[i].x; o[1] = r.p[i].y; o[2] = r.p[i].z; o[3] = r.quat[i].x; o[4] = r.quat[i].y; o[5] = r.quat[i].z; o[6] = r.quat[i].w; }
+}
+void urgo_ik(const double* q, const double* target7, double* out6) {
+  World w(ENV_BALL); std::memcpy(w.rob.q, q, sizeof(double) * NDOF);
+  w.ik(V3(target7[0], target7[1], target7[2]), Q4(target7[3], target7[4], target7[5], target7[6]), out6);
+}
+void urgo_gripper_center(const double* q, double* out3) {
+  World w(ENV_BALL); std::memcpy(w.rob.q, q, sizeof(double) * NDOF);
+  V3 c = w.gripper_center(); out3[0] = c.x; out3[1] = c.y; out3[2] = c.z;
+}
+// free (unconstrained) joint accelerations by the 19-link ABA and M^-1 tau via the cached articulated inertias
+void urgo_forward_dynamics(const double* q, const double* qd, double gz, double* qdd) {
+  Robot r; std::memcpy(r.q, q, sizeof(double) * NDOF); std::memcpy(r.qd, qd, sizeof(double) * NDOF); r.fk(); r.aba(gz, qdd);
+}
+void urgo_minv(const double* q, double* out144) {
+  Robot r; std::memcpy(r.q, q, sizeof(double) * NDOF); r.fk(); double qdd[NDOF]; r.aba(0.0, qdd);
+  for (int d = 0; d < NDOF; d++) { double tau[NDOF] = {0}; tau[d] = 1; double col[NDOF]; r.minv_mul(tau, col); for (int k = 0; k < NDOF; k++) out144[k * NDOF + d] = col[k]; }
+}
+void urgo_euler_from_quat(const double* q, double* e) { V3 v = euler_from_quat(Q4(q[0], q[1], q[2], q[3])); e[0] = v.x; e[1] = v.y; e[2] = v.z; }
+void urgo_quat_from_euler(const double* e, double* q) { Q4 v = quat_from_euler(e[0], e[1], e[2]); q[0] = v.x; q[1] = v.y; q[2] = v.z; q[3] = v.w; }
+void urgo_quat_mul(const double* a, const double* b, double* o) { Q4 v = Q4(a[0], a[1], a[2], a[3]) * Q4(b[0], b[1], b[2], b[3]); o[0] = v.x; o[1] = v.y; o[2] = v.z; o[3] = v.w; }
+double urgo_geometric_distance_reward(double v, double ts, double tm) { return geometric_distance_reward(v, ts, tm); }
+double urgo_gripper_angle(double len) { return gripper_angle(len); }
+double urgo_urand(uint64_t seed, uint32_t env, uint32_t episode, uint32_t draw) { return urand(seed, env, episode, draw); }
+// box-box narrowphase: a,b = [c3, R9 row-major, h3]; out = [n][10] posA3 posB3 n3 dist
+int urgo_box_box(const double* a, const double* b, double margin, double* out) {
+  BoxW A, B; A.c = V3(a[0], a[1], a[2]); for (int i = 0; i < 9; i++) A.R.m[i] = a[3 + i]; A.h = V3(a[12], a[13], a[14]);
+  B.c = V3(b[0], b[1], b[2]); for (int i = 0; i < 9; i++) B.R.m[i] = b[3 + i]; B.h = V3(b[12], b[13], b[14]);
+  CPoint p[4]; int n = box_box(A, B, margin, p);
+  for (int i = 0; i < n; i++) { double* o = out + 10 * i; o[0] = p[i].posA.x; o[1] = p[i].posA.y; o[2] = p[i].posA.z; o[3] = p[i].posB.x; o[4] = p[i].posB.y; o[5] = p[i].posB.z; o[6] = p[i].n.x; o[7] = p[i].n.y; o[8] = p[i].n.z; o[9] = p[i].dist; }
+  return n;
+}
+
+}  // extern "C"
