@@ -1,0 +1,103 @@
+/*
+ * urgym_b200 — C ABI of the B200-native batched physics backend for the URGym step path.
+ *
+ * The reference has no FFI: its hot path sits behind the Gymnasium Env interface and, below that, behind the
+ * module-level pybullet calls listed in SURVEY.md §2a. Each entry point below names the reference interface it
+ * replaces (paths under /root/reference). Conventions: every function returns 0 on success or a negative URGYM_E_*
+ * code (text via urgym_last_error); no exception crosses the boundary; all `*_dev` pointers are device memory owned
+ * by the caller (e.g. torch tensors) on the handle's device; calls are asynchronous on `stream` (a cudaStream_t
+ * passed as void*); one host thread per handle at a time; the library never frees caller buffers.
+ *
+ * There is no CPU fallback: every call fails with URGYM_E_CUDA when no sm_100 device is usable.
+ */
+#ifndef URGYM_B200_H
+#define URGYM_B200_H
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef struct urgym_env_s* urgym_handle;
+
+enum { URGYM_BALL_BALANCE = 0, URGYM_TWO_BALLS_BALANCE = 1, URGYM_CUBES_PUSH = 2, URGYM_CUBES_GRASP = 3, URGYM_GOLF = 4 };
+enum { URGYM_OK = 0, URGYM_E_ARG = -1, URGYM_E_CUDA = -2, URGYM_E_STATE = -3 };
+enum { URGYM_STATE_FLOATS = 96, URGYM_MAX_CONTACTS = 16, URGYM_NUM_LINKS = 19, URGYM_NUM_DOF = 12 };
+
+/* Static facts per env type: urgym/envs/__init__.py:10-44 (max_episode_steps) and each env's spaces, e.g.
+ * urgym/envs/env_ball_balance_v0.py:52-54. */
+int urgym_obs_dim(int env_type);
+int urgym_act_dim(int env_type);
+int urgym_max_episode_steps(int env_type);
+int urgym_num_shapes(int env_type);
+/* body: 0 robot, 1..3 free body, -1 static; link: Bullet link index on the robot or sub-shape id otherwise */
+int urgym_shape_info(int env_type, int shape, int* body, int* link);
+
+/* Replaces Env.__init__ + UR5Robotiq85.load (env_ball_balance_v0.py:34-80, urgym/base/robot.py:39-77,178-211):
+ * builds `num_envs` independent worlds resident in HBM on `device`. `env_index_offset` is the global index of this
+ * shard's first env (the RNG is keyed on seed, global env index, episode and draw, so results do not depend on the
+ * shard layout). reward_sparse mirrors reward_type='sparse' (env_cubes_push_v0.py:159, env_golf_v0.py:151,163). */
+int urgym_create(int env_type, int num_envs, int device, uint64_t seed, int env_index_offset, int reward_sparse,
+                 urgym_handle* out);
+int urgym_destroy(urgym_handle h);
+
+/* Replaces Env.reset (env_ball_balance_v0.py:145-170 and the four siblings; robot.py:85-101).
+ * mask_dev: uint8[N], nullable = all. draws_dev: float[N,4] uniforms in [0,1) replacing the reference's global-random
+ * draws (env_ball_balance_v0.py:193-194 etc.), nullable = counter-based RNG. obs_dev: float[N,obs_dim].
+ * nticks_dev: int32[N] physics ticks spent, nullable. */
+int urgym_reset(urgym_handle h, const uint8_t* mask_dev, const float* draws_dev, float* obs_dev, int32_t* nticks_dev,
+                void* stream);
+
+/* Replaces Env.step (env_ball_balance_v0.py:105-134 and siblings): IK -> joint motors -> wait_until_stable (1..480
+ * stepSimulation ticks) -> contact predicates -> reward / terminated / observation, plus the TimeLimit wrapper's
+ * `truncated`, and, when autoreset != 0, the reset of finished envs (obs_dev then holds the new episode's first
+ * observation and final_obs_dev the last one of the old episode).
+ * action_dev float[N,act_dim]; u_dev float[N] selector uniform for CubesGrasp (env_cubes_grasp_v0.py:127-130),
+ * nullable = RNG; draws_dev as in urgym_reset; outputs: obs float[N,obs_dim], reward float[N], terminated /
+ * truncated / success uint8[N], final_obs float[N,obs_dim] (nullable), nticks int32[N,2] = {settle ticks of the
+ * action, ticks of the auto-reset} (nullable). */
+int urgym_step(urgym_handle h, const float* action_dev, const float* u_dev, const float* draws_dev, float* obs_dev,
+               float* reward_dev, uint8_t* terminated_dev, uint8_t* truncated_dev, uint8_t* success_dev,
+               float* final_obs_dev, int32_t* nticks_dev, int autoreset, void* stream);
+
+/* Same call with HOST buffers: copies inputs host->device and results device->host on the handle's stream and
+ * synchronises. This is the entry the single-env Gymnasium shim and bench.py's e2e leg use. */
+int urgym_step_host(urgym_handle h, const float* action, const float* u, const float* draws, float* obs, float* reward,
+                    uint8_t* terminated, uint8_t* truncated, uint8_t* success, float* final_obs, int32_t* nticks,
+                    int autoreset);
+int urgym_reset_host(urgym_handle h, const uint8_t* mask, const float* draws, float* obs, int32_t* nticks);
+
+/* Snapshot / restore of the per-env state records, float[N,URGYM_STATE_FLOATS] (integers stored as exact floats).
+ * Stands in for pybullet's saveState/restoreState, unused by the reference, needed for identical-initial-state runs. */
+int urgym_get_state(urgym_handle h, float* state_dev, void* stream);
+int urgym_set_state(urgym_handle h, const float* state_dev, void* stream);
+
+/* Replaces getContactPoints as the envs use it (env_cubes_push_v0.py:177,186; env_cubes_grasp_v0.py:210;
+ * env_golf_v0.py:187-206): the manifold points of the last tick of the last step, as shape-index pairs.
+ * pairs_dev int32[N,URGYM_MAX_CONTACTS,2] (-1 padded), count_dev int32[N]. */
+int urgym_contacts(urgym_handle h, int32_t* pairs_dev, int32_t* count_dev, void* stream);
+
+/* Raw stepSimulation: `nticks` physics ticks on every env with the current motor targets, no env logic. */
+int urgym_tick(urgym_handle h, int nticks, void* stream);
+
+/* Stand-alone kinematics on `n` joint vectors (no handle state is touched):
+ * urgym_fk replaces getLinkState(robot, i)[4:6] for all 19 links: q float[n,12] -> pose float[n,19,7] (xyz, quat xyzw).
+ * urgym_ik replaces calculateInverseKinematics as robot.py:119-121 calls it: q float[n,12], target float[n,7]
+ * -> arm joint targets float[n,6].
+ * urgym_gripper_center replaces get_gripper_geometrical_center (env_ball_balance_v0.py:249-275): -> float[n,3]. */
+int urgym_fk(int device, int n, const float* q_dev, float* pose_dev, void* stream);
+int urgym_ik(int device, int n, const float* q_dev, const float* target_dev, float* out_dev, void* stream);
+int urgym_gripper_center(int device, int n, const float* q_dev, float* out_dev, void* stream);
+
+/* Episode statistics accumulated on device since creation: {episodes, return sum, length sum, successes, env steps,
+ * physics ticks}. Synchronises the handle's last stream. (Optional NCCL reduction happens in the Python host.) */
+int urgym_stats(urgym_handle h, double out[6]);
+/* Kernel launches issued by this library in this process (bench.py's gpu_launches claim). */
+long long urgym_launch_count(void);
+const char* urgym_last_error(void);
+
+#ifdef __cplusplus
+}
+#endif
+#endif

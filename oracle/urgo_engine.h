@@ -523,6 +523,7 @@ struct World {
   // seeded from the current joint angles, <= 20 iterations [recalled]. Returns 6 arm targets.
   void ik(V3 tpos, Q4 tq, double* out6) {
     Robot r = rob;
+    tq = normalized(tq);  // pybullet moves the target into the base frame through a btTransform, which normalises it [recalled]
     double diff = 1e30;
     for (int it = 0; it < BP_IK_ITERS && diff > BP_IK_RESIDUAL; it++) {
       r.fk();

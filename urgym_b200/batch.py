@@ -1,0 +1,129 @@
+"""Device-resident batch of URGym worlds: thin torch-facing wrapper over the C ABI (no host sync on the step path)."""
+import ctypes as C
+
+import torch
+
+from . import _lib
+from ._lib import ENV_TYPES, MAX_CONTACTS, NUM_LINKS, STATE_FLOATS, check
+
+
+def _ptr(t):
+    return None if t is None else C.c_void_p(t.data_ptr())
+
+
+def _f32(t, dev, shape=None):
+    if t is None:
+        return None
+    t = torch.as_tensor(t, dtype=torch.float32, device=dev).contiguous()
+    if shape is not None:
+        t = t.reshape(shape)
+    return t
+
+
+def _stream(dev):
+    return C.c_void_p(torch.cuda.current_stream(dev).cuda_stream)
+
+
+class EnvBatch:
+    """`num_envs` independent instances of one env type on one GPU."""
+
+    def __init__(self, env, num_envs, device=0, seed=0, env_index_offset=0, reward_sparse=False):
+        if not torch.cuda.is_available():
+            raise _lib.UrgymError('CUDA is not available: urgym_b200 has no CPU path')
+        self.L = _lib.lib()
+        self.env_type = ENV_TYPES[env] if isinstance(env, str) else int(env)
+        self.num_envs = int(num_envs)
+        self.device = torch.device('cuda', device if isinstance(device, int) else torch.device(device).index or 0)
+        self.obs_dim = self.L.urgym_obs_dim(self.env_type)
+        self.act_dim = self.L.urgym_act_dim(self.env_type)
+        self.max_episode_steps = self.L.urgym_max_episode_steps(self.env_type)
+        h = C.c_void_p()
+        check(self.L.urgym_create(self.env_type, self.num_envs, self.device.index, seed, env_index_offset, int(reward_sparse), C.byref(h)))
+        self.h = h
+        n, d = self.num_envs, self.device
+        self.obs = torch.zeros(n, self.obs_dim, device=d)
+        self.final_obs = torch.zeros(n, self.obs_dim, device=d)
+        self.reward = torch.zeros(n, device=d)
+        self.terminated = torch.zeros(n, dtype=torch.uint8, device=d)
+        self.truncated = torch.zeros(n, dtype=torch.uint8, device=d)
+        self.success = torch.zeros(n, dtype=torch.uint8, device=d)
+        self.nticks = torch.zeros(n, 2, dtype=torch.int32, device=d)
+        self.reset_ticks = torch.zeros(n, dtype=torch.int32, device=d)
+
+    def close(self):
+        if getattr(self, 'h', None) is not None and self.h:
+            self.L.urgym_destroy(self.h)
+            self.h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def reset(self, mask=None, draws=None):
+        d = self.device
+        m = None if mask is None else torch.as_tensor(mask, device=d).to(torch.uint8).contiguous()
+        dr = _f32(draws, d, (self.num_envs, 4))
+        check(self.L.urgym_reset(self.h, _ptr(m), _ptr(dr), _ptr(self.obs), _ptr(self.reset_ticks), _stream(d)))
+        return self.obs
+
+    def step(self, action, u=None, draws=None, autoreset=True):
+        d = self.device
+        a = _f32(action, d, (self.num_envs, self.act_dim))
+        uu = _f32(u, d, (self.num_envs,))
+        dr = _f32(draws, d, (self.num_envs, 4))
+        check(self.L.urgym_step(self.h, _ptr(a), _ptr(uu), _ptr(dr), _ptr(self.obs), _ptr(self.reward), _ptr(self.terminated),
+                                _ptr(self.truncated), _ptr(self.success), _ptr(self.final_obs), _ptr(self.nticks), int(autoreset), _stream(d)))
+        return self.obs, self.reward, self.terminated, self.truncated, self.success
+
+    def tick(self, n=1):
+        check(self.L.urgym_tick(self.h, int(n), _stream(self.device)))
+
+    def get_state(self):
+        s = torch.empty(self.num_envs, STATE_FLOATS, device=self.device)
+        check(self.L.urgym_get_state(self.h, _ptr(s), _stream(self.device)))
+        return s
+
+    def set_state(self, s):
+        s = _f32(s, self.device, (self.num_envs, STATE_FLOATS))
+        check(self.L.urgym_set_state(self.h, _ptr(s), _stream(self.device)))
+        torch.cuda.current_stream(self.device).synchronize()
+
+    def contacts(self):
+        pairs = torch.empty(self.num_envs, MAX_CONTACTS, 2, dtype=torch.int32, device=self.device)
+        cnt = torch.empty(self.num_envs, dtype=torch.int32, device=self.device)
+        check(self.L.urgym_contacts(self.h, _ptr(pairs), _ptr(cnt), _stream(self.device)))
+        return pairs, cnt
+
+    def stats(self):
+        out = (C.c_double * 6)()
+        check(self.L.urgym_stats(self.h, out))
+        return dict(zip(('episodes', 'return_sum', 'length_sum', 'successes', 'env_steps', 'ticks'), list(out)))
+
+
+def forward_kinematics(q, device=0):
+    """q [n,12] -> link poses [n,19,7] (xyz, quat xyzw); replaces getLinkState for every link."""
+    dev = torch.device('cuda', device)
+    q = _f32(q, dev).reshape(-1, 12)
+    out = torch.empty(q.shape[0], NUM_LINKS, 7, device=dev)
+    check(_lib.lib().urgym_fk(device, q.shape[0], _ptr(q), _ptr(out), _stream(dev)))
+    return out
+
+
+def inverse_kinematics(q, target, device=0):
+    """q [n,12], target [n,7] -> arm joint targets [n,6]; replaces calculateInverseKinematics (robot.py:119-121)."""
+    dev = torch.device('cuda', device)
+    q = _f32(q, dev).reshape(-1, 12)
+    t = _f32(target, dev).reshape(-1, 7)
+    out = torch.empty(q.shape[0], 6, device=dev)
+    check(_lib.lib().urgym_ik(device, q.shape[0], _ptr(q), _ptr(t), _ptr(out), _stream(dev)))
+    return out
+
+
+def gripper_center(q, device=0):
+    dev = torch.device('cuda', device)
+    q = _f32(q, dev).reshape(-1, 12)
+    out = torch.empty(q.shape[0], 3, device=dev)
+    check(_lib.lib().urgym_gripper_center(device, q.shape[0], _ptr(q), _ptr(out), _stream(dev)))
+    return out

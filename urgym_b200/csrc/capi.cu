@@ -1,0 +1,256 @@
+// C ABI of liburgym_b200.so (declared in include/urgym_b200.h). Host code only orchestrates: device memory, streams,
+// launches. No CPU physics exists in this library: without a usable CUDA device every call fails.
+#include <atomic>
+#include <cstdio>
+#include <cstring>
+#include <cstdlib>
+#include <string>
+#include <vector>
+
+#include "../../include/urgym_b200.h"
+#include "kernels.cuh"
+
+namespace {
+
+thread_local std::string g_err;
+std::atomic<long long> g_launches{0};
+
+int fail(int code, const std::string& msg) { g_err = msg; return code; }
+#define CK(call)                                                                                        \
+  do {                                                                                                  \
+    cudaError_t e_ = (call);                                                                            \
+    if (e_ != cudaSuccess) return fail(URGYM_E_CUDA, std::string(#call) + ": " + cudaGetErrorString(e_)); \
+  } while (0)
+
+struct ModelCache { DevModel host; DevModel* dev = nullptr; int device = -1; };
+
+}  // namespace
+
+struct urgym_env_s {
+  int env_type, N, device, gidx0, sparse;
+  uint64_t seed;
+  DevModel hmodel; DevModel* dmodel = nullptr;
+  float* state = nullptr; int32_t* contacts = nullptr; int32_t* ccount = nullptr; double* stats = nullptr;
+  // staging for the *_host entry points
+  float *d_action = nullptr, *d_u = nullptr, *d_draws = nullptr, *d_obs = nullptr, *d_final = nullptr, *d_reward = nullptr;
+  uint8_t *d_term = nullptr, *d_trunc = nullptr, *d_succ = nullptr, *d_mask = nullptr; int32_t* d_nticks = nullptr;
+  cudaStream_t own_stream = nullptr, last_stream = nullptr;
+};
+
+namespace {
+
+template <int ENV>
+int launch_env(urgym_handle h, const KParams& P, cudaStream_t st) {
+  static bool attr_done[16] = {false};
+  size_t smem = sizeof(Smem);
+  if (!attr_done[h->device & 15]) {
+    CK(cudaFuncSetAttribute(env_kernel<ENV>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    CK(cudaFuncSetAttribute(env_kernel<ENV>, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared));
+    attr_done[h->device & 15] = true;
+  }
+  env_kernel<ENV><<<h->N, 32, smem, st>>>(P);
+  g_launches++;
+  CK(cudaGetLastError());
+  h->last_stream = st;
+  return URGYM_OK;
+}
+
+int launch(urgym_handle h, KParams& P, void* stream) {
+  CK(cudaSetDevice(h->device));
+  P.model = h->dmodel; P.state = h->state; P.N = h->N; P.contacts = h->contacts; P.ccount = h->ccount; P.stats = h->stats;
+  P.seed = h->seed; P.gidx0 = h->gidx0; P.sparse = h->sparse;
+  cudaStream_t st = (cudaStream_t)stream;  // NULL = the legacy default stream, as in the CUDA runtime
+  switch (h->env_type) {
+    case 0: return launch_env<0>(h, P, st);
+    case 1: return launch_env<1>(h, P, st);
+    case 2: return launch_env<2>(h, P, st);
+    case 3: return launch_env<3>(h, P, st);
+    default: return launch_env<4>(h, P, st);
+  }
+}
+
+struct KinCtx { DevModel* dmodel = nullptr; };
+KinCtx g_kin[16];
+int kin_model(int device, DevModel** out) {
+  if (device < 0 || device >= 16) return fail(URGYM_E_ARG, "device out of range");
+  CK(cudaSetDevice(device));
+  if (!g_kin[device].dmodel) {
+    DevModel hm; if (build_model(0, &hm)) return fail(URGYM_E_ARG, "model build failed");
+    CK(cudaMalloc(&g_kin[device].dmodel, sizeof(DevModel)));
+    CK(cudaMemcpy(g_kin[device].dmodel, &hm, sizeof(DevModel), cudaMemcpyHostToDevice));
+  }
+  *out = g_kin[device].dmodel;
+  return URGYM_OK;
+}
+
+}  // namespace
+
+extern "C" {
+
+int urgym_obs_dim(int t) { DevModel m; return build_model(t, &m) ? URGYM_E_ARG : m.obs_dim; }
+int urgym_act_dim(int t) { DevModel m; return build_model(t, &m) ? URGYM_E_ARG : m.act_dim; }
+int urgym_max_episode_steps(int t) { DevModel m; return build_model(t, &m) ? URGYM_E_ARG : m.max_steps; }
+int urgym_num_shapes(int t) { DevModel m; return build_model(t, &m) ? URGYM_E_ARG : m.nshapes; }
+int urgym_shape_info(int t, int shape, int* body, int* link) {
+  DevModel m; if (build_model(t, &m) || shape < 0 || shape >= m.nshapes) return fail(URGYM_E_ARG, "bad shape index");
+  *body = m.shapes[shape].body; *link = m.shapes[shape].link; return URGYM_OK;
+}
+
+int urgym_create(int env_type, int num_envs, int device, uint64_t seed, int env_index_offset, int reward_sparse, urgym_handle* out) {
+  if (!out || num_envs <= 0 || env_type < 0 || env_type > 4) return fail(URGYM_E_ARG, "urgym_create: bad arguments");
+  int ndev = 0;
+  if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev == 0) return fail(URGYM_E_CUDA, "no CUDA device: urgym_b200 has no CPU path");
+  if (device < 0 || device >= ndev) return fail(URGYM_E_ARG, "urgym_create: device out of range");
+  CK(cudaSetDevice(device));
+  if (getenv("URGYM_STACK")) CK(cudaDeviceSetLimit(cudaLimitStackSize, (size_t)atoi(getenv("URGYM_STACK"))));
+  urgym_handle h = new urgym_env_s;
+  h->env_type = env_type; h->N = num_envs; h->device = device; h->seed = seed; h->gidx0 = env_index_offset; h->sparse = reward_sparse;
+  if (build_model(env_type, &h->hmodel)) { delete h; return fail(URGYM_E_ARG, "model build failed"); }
+  size_t n = (size_t)num_envs; int od = h->hmodel.obs_dim, ad = h->hmodel.act_dim;
+  CK(cudaMalloc(&h->dmodel, sizeof(DevModel)));
+  CK(cudaMemcpy(h->dmodel, &h->hmodel, sizeof(DevModel), cudaMemcpyHostToDevice));
+  CK(cudaMalloc(&h->state, n * UG_STATE * sizeof(float)));
+  CK(cudaMalloc(&h->contacts, n * UG_MAXC * 2 * sizeof(int32_t)));
+  CK(cudaMalloc(&h->ccount, n * sizeof(int32_t)));
+  CK(cudaMalloc(&h->stats, 8 * sizeof(double)));
+  CK(cudaMemset(h->stats, 0, 8 * sizeof(double)));
+  CK(cudaMemset(h->contacts, 0xff, n * UG_MAXC * 2 * sizeof(int32_t)));
+  CK(cudaMemset(h->ccount, 0, n * sizeof(int32_t)));
+  CK(cudaMalloc(&h->d_action, n * ad * sizeof(float))); CK(cudaMalloc(&h->d_u, n * sizeof(float))); CK(cudaMalloc(&h->d_draws, n * 4 * sizeof(float)));
+  CK(cudaMalloc(&h->d_obs, n * od * sizeof(float))); CK(cudaMalloc(&h->d_final, n * od * sizeof(float))); CK(cudaMalloc(&h->d_reward, n * sizeof(float)));
+  CK(cudaMalloc(&h->d_term, n)); CK(cudaMalloc(&h->d_trunc, n)); CK(cudaMalloc(&h->d_succ, n)); CK(cudaMalloc(&h->d_mask, n));
+  CK(cudaMalloc(&h->d_nticks, n * 2 * sizeof(int32_t)));
+  CK(cudaStreamCreateWithFlags(&h->own_stream, cudaStreamNonBlocking));
+  std::vector<float> init(n * UG_STATE, 0.f);
+  for (size_t i = 0; i < n; i++) { float* r = init.data() + i * UG_STATE; r[37] = 1.f; for (int b = 0; b < UG_MAXFREE; b++) r[38 + 13 * b + 6] = 1.f; }
+  CK(cudaMemcpy(h->state, init.data(), init.size() * sizeof(float), cudaMemcpyHostToDevice));
+  *out = h;
+  return URGYM_OK;
+}
+
+int urgym_destroy(urgym_handle h) {
+  if (!h) return URGYM_OK;
+  cudaSetDevice(h->device);
+  cudaDeviceSynchronize();
+  void* ptrs[] = {h->dmodel, h->state, h->contacts, h->ccount, h->stats, h->d_action, h->d_u, h->d_draws, h->d_obs, h->d_final, h->d_reward, h->d_term, h->d_trunc, h->d_succ, h->d_mask, h->d_nticks};
+  for (void* p : ptrs) if (p) cudaFree(p);
+  if (h->own_stream) cudaStreamDestroy(h->own_stream);
+  delete h;
+  return URGYM_OK;
+}
+
+int urgym_reset(urgym_handle h, const uint8_t* mask_dev, const float* draws_dev, float* obs_dev, int32_t* nticks_dev, void* stream) {
+  if (!h || !obs_dev) return fail(URGYM_E_ARG, "urgym_reset: null argument");
+  KParams P; std::memset(&P, 0, sizeof(P));
+  P.mode = MODE_RESET; P.mask = mask_dev; P.draws = draws_dev; P.obs = obs_dev; P.nticks = nticks_dev;
+  return launch(h, P, stream);
+}
+
+int urgym_step(urgym_handle h, const float* action_dev, const float* u_dev, const float* draws_dev, float* obs_dev, float* reward_dev,
+               uint8_t* terminated_dev, uint8_t* truncated_dev, uint8_t* success_dev, float* final_obs_dev, int32_t* nticks_dev,
+               int autoreset, void* stream) {
+  if (!h || !action_dev || !obs_dev || !reward_dev || !terminated_dev || !truncated_dev || !success_dev) return fail(URGYM_E_ARG, "urgym_step: null argument");
+  KParams P; std::memset(&P, 0, sizeof(P));
+  P.mode = MODE_STEP; P.action = action_dev; P.u = u_dev; P.draws = draws_dev; P.obs = obs_dev; P.reward = reward_dev;
+  P.term = terminated_dev; P.trunc = truncated_dev; P.succ = success_dev; P.final_obs = final_obs_dev; P.nticks = nticks_dev; P.autoreset = autoreset;
+  return launch(h, P, stream);
+}
+
+int urgym_tick(urgym_handle h, int nticks, void* stream) {
+  if (!h || nticks <= 0) return fail(URGYM_E_ARG, "urgym_tick: bad arguments");
+  KParams P; std::memset(&P, 0, sizeof(P));
+  P.mode = MODE_TICKS; P.raw_ticks = nticks;
+  return launch(h, P, stream);
+}
+
+int urgym_step_host(urgym_handle h, const float* action, const float* u, const float* draws, float* obs, float* reward, uint8_t* terminated,
+                    uint8_t* truncated, uint8_t* success, float* final_obs, int32_t* nticks, int autoreset) {
+  if (!h || !action || !obs || !reward || !terminated || !truncated || !success) return fail(URGYM_E_ARG, "urgym_step_host: null argument");
+  CK(cudaSetDevice(h->device));
+  size_t n = (size_t)h->N; int od = h->hmodel.obs_dim, ad = h->hmodel.act_dim; cudaStream_t st = h->own_stream;
+  CK(cudaMemcpyAsync(h->d_action, action, n * ad * sizeof(float), cudaMemcpyHostToDevice, st));
+  if (u) CK(cudaMemcpyAsync(h->d_u, u, n * sizeof(float), cudaMemcpyHostToDevice, st));
+  if (draws) CK(cudaMemcpyAsync(h->d_draws, draws, n * 4 * sizeof(float), cudaMemcpyHostToDevice, st));
+  int rc = urgym_step(h, h->d_action, u ? h->d_u : nullptr, draws ? h->d_draws : nullptr, h->d_obs, h->d_reward, h->d_term, h->d_trunc, h->d_succ,
+                      h->d_final, h->d_nticks, autoreset, st);
+  if (rc) return rc;
+  CK(cudaMemcpyAsync(obs, h->d_obs, n * od * sizeof(float), cudaMemcpyDeviceToHost, st));
+  CK(cudaMemcpyAsync(reward, h->d_reward, n * sizeof(float), cudaMemcpyDeviceToHost, st));
+  CK(cudaMemcpyAsync(terminated, h->d_term, n, cudaMemcpyDeviceToHost, st));
+  CK(cudaMemcpyAsync(truncated, h->d_trunc, n, cudaMemcpyDeviceToHost, st));
+  CK(cudaMemcpyAsync(success, h->d_succ, n, cudaMemcpyDeviceToHost, st));
+  if (final_obs) CK(cudaMemcpyAsync(final_obs, h->d_final, n * od * sizeof(float), cudaMemcpyDeviceToHost, st));
+  if (nticks) CK(cudaMemcpyAsync(nticks, h->d_nticks, n * 2 * sizeof(int32_t), cudaMemcpyDeviceToHost, st));
+  CK(cudaStreamSynchronize(st));
+  return URGYM_OK;
+}
+
+int urgym_reset_host(urgym_handle h, const uint8_t* mask, const float* draws, float* obs, int32_t* nticks) {
+  if (!h || !obs) return fail(URGYM_E_ARG, "urgym_reset_host: null argument");
+  CK(cudaSetDevice(h->device));
+  size_t n = (size_t)h->N; int od = h->hmodel.obs_dim; cudaStream_t st = h->own_stream;
+  if (mask) CK(cudaMemcpyAsync(h->d_mask, mask, n, cudaMemcpyHostToDevice, st));
+  if (draws) CK(cudaMemcpyAsync(h->d_draws, draws, n * 4 * sizeof(float), cudaMemcpyHostToDevice, st));
+  if (mask) CK(cudaMemcpyAsync(h->d_obs, obs, n * od * sizeof(float), cudaMemcpyHostToDevice, st));  // unmasked rows keep the caller's values
+  int rc = urgym_reset(h, mask ? h->d_mask : nullptr, draws ? h->d_draws : nullptr, h->d_obs, h->d_nticks, st);
+  if (rc) return rc;
+  CK(cudaMemcpyAsync(obs, h->d_obs, n * od * sizeof(float), cudaMemcpyDeviceToHost, st));
+  if (nticks) CK(cudaMemcpyAsync(nticks, h->d_nticks, n * sizeof(int32_t), cudaMemcpyDeviceToHost, st));
+  CK(cudaStreamSynchronize(st));
+  return URGYM_OK;
+}
+
+int urgym_get_state(urgym_handle h, float* state_dev, void* stream) {
+  if (!h || !state_dev) return fail(URGYM_E_ARG, "urgym_get_state: null argument");
+  CK(cudaSetDevice(h->device));
+  cudaStream_t st = (cudaStream_t)stream;  // NULL = the legacy default stream, as in the CUDA runtime
+  CK(cudaMemcpyAsync(state_dev, h->state, (size_t)h->N * UG_STATE * sizeof(float), cudaMemcpyDeviceToDevice, st));
+  h->last_stream = st; return URGYM_OK;
+}
+int urgym_set_state(urgym_handle h, const float* state_dev, void* stream) {
+  if (!h || !state_dev) return fail(URGYM_E_ARG, "urgym_set_state: null argument");
+  CK(cudaSetDevice(h->device));
+  cudaStream_t st = (cudaStream_t)stream;  // NULL = the legacy default stream, as in the CUDA runtime
+  CK(cudaMemcpyAsync(h->state, state_dev, (size_t)h->N * UG_STATE * sizeof(float), cudaMemcpyDeviceToDevice, st));
+  h->last_stream = st; return URGYM_OK;
+}
+int urgym_contacts(urgym_handle h, int32_t* pairs_dev, int32_t* count_dev, void* stream) {
+  if (!h || !pairs_dev || !count_dev) return fail(URGYM_E_ARG, "urgym_contacts: null argument");
+  CK(cudaSetDevice(h->device));
+  cudaStream_t st = (cudaStream_t)stream;  // NULL = the legacy default stream, as in the CUDA runtime
+  CK(cudaMemcpyAsync(pairs_dev, h->contacts, (size_t)h->N * UG_MAXC * 2 * sizeof(int32_t), cudaMemcpyDeviceToDevice, st));
+  CK(cudaMemcpyAsync(count_dev, h->ccount, (size_t)h->N * sizeof(int32_t), cudaMemcpyDeviceToDevice, st));
+  h->last_stream = st; return URGYM_OK;
+}
+
+int urgym_fk(int device, int n, const float* q_dev, float* pose_dev, void* stream) {
+  if (n <= 0 || !q_dev || !pose_dev) return fail(URGYM_E_ARG, "urgym_fk: bad arguments");
+  DevModel* dm; int rc = kin_model(device, &dm); if (rc) return rc;
+  fk_kernel<<<(n + 63) / 64, 64, 0, (cudaStream_t)stream>>>(dm, n, q_dev, pose_dev); g_launches++;
+  CK(cudaGetLastError()); return URGYM_OK;
+}
+int urgym_ik(int device, int n, const float* q_dev, const float* target_dev, float* out_dev, void* stream) {
+  if (n <= 0 || !q_dev || !target_dev || !out_dev) return fail(URGYM_E_ARG, "urgym_ik: bad arguments");
+  DevModel* dm; int rc = kin_model(device, &dm); if (rc) return rc;
+  ik_kernel<<<(n + 63) / 64, 64, 0, (cudaStream_t)stream>>>(dm, n, q_dev, target_dev, out_dev); g_launches++;
+  CK(cudaGetLastError()); return URGYM_OK;
+}
+int urgym_gripper_center(int device, int n, const float* q_dev, float* out_dev, void* stream) {
+  if (n <= 0 || !q_dev || !out_dev) return fail(URGYM_E_ARG, "urgym_gripper_center: bad arguments");
+  DevModel* dm; int rc = kin_model(device, &dm); if (rc) return rc;
+  CK(cudaFuncSetAttribute(gripper_center_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(Smem)));
+  gripper_center_kernel<<<n, 32, sizeof(Smem), (cudaStream_t)stream>>>(dm, n, q_dev, out_dev); g_launches++;
+  CK(cudaGetLastError()); return URGYM_OK;
+}
+
+int urgym_stats(urgym_handle h, double out[6]) {
+  if (!h || !out) return fail(URGYM_E_ARG, "urgym_stats: null argument");
+  CK(cudaSetDevice(h->device));
+  if (h->last_stream) CK(cudaStreamSynchronize(h->last_stream));
+  CK(cudaMemcpy(out, h->stats, 6 * sizeof(double), cudaMemcpyDeviceToHost));
+  return URGYM_OK;
+}
+long long urgym_launch_count(void) { return g_launches.load(); }
+const char* urgym_last_error(void) { return g_err.c_str(); }
+
+}  // extern "C"

@@ -1,0 +1,280 @@
+// The fused env kernel: one launch advances every env by one gym step (action -> IK -> 1..480 ticks -> epilogue ->
+// optional in-kernel auto-reset). State crosses HBM once in and once out per gym step.
+#pragma once
+#include "dev_env.cuh"
+
+template <int ENV>
+UG_DEV void observe(Smem& s, const DevModel& M, float* o, int lane) {
+  // caller guarantees fresh fk_bodies(); every lane computes, lane 0 writes
+  f3 ep; m3 eR; ee_pose(s, M, ep, eR);
+  float v[17];
+  if (ENV == 0 || ENV == 1) {
+    f3 e = euler_from_quat(mkq(s.fquat[0][0], s.fquat[0][1], s.fquat[0][2], s.fquat[0][3]));
+    v[0] = e.x; v[1] = e.y; v[2] = e.z;
+#pragma unroll
+    for (int b = 1; b <= (ENV == 0 ? 1 : 2); b++) { f3 d = ld3(s.fpos[0]) - ld3(s.fpos[b]); v[3 * b] = d.x; v[3 * b + 1] = d.y; v[3 * b + 2] = d.z; }
+  } else if (ENV == 2) {
+    v[0] = ep.x; v[1] = ep.y; v[2] = ep.z;
+#pragma unroll
+    for (int b = 0; b < 2; b++) { v[3 + 3 * b] = s.fpos[b][0]; v[4 + 3 * b] = s.fpos[b][1]; v[5 + 3 * b] = s.fpos[b][2]; }
+  } else if (ENV == 3) {
+    q4 eq = link_quat_chain(s.q, M, 7);
+    v[0] = (s.flags & FL_APPROACHED) ? 1.f : 0.f; v[1] = (s.flags & FL_GRASPED) ? 1.f : 0.f;
+    v[2] = ep.x; v[3] = ep.y; v[4] = ep.z; v[5] = eq.x; v[6] = eq.y; v[7] = eq.z; v[8] = eq.w;
+    v[9] = gripper_opening(s, M);
+    v[10] = s.fpos[0][0]; v[11] = s.fpos[0][1]; v[12] = s.fpos[0][2];
+    v[13] = s.fquat[0][0]; v[14] = s.fquat[0][1]; v[15] = s.fquat[0][2]; v[16] = s.fquat[0][3];
+  } else {
+    f3 st = club_foot(s), b = ld3(s.fpos[1]), h = mk3(0.f, -0.6f, 0.02f);
+    f3 d1 = st - b, d2 = h - b;
+    v[0] = st.x; v[1] = st.y; v[2] = st.z; v[3] = d1.x; v[4] = d1.y; v[5] = d1.z; v[6] = d2.x; v[7] = d2.y; v[8] = d2.z;
+  }
+  constexpr int OD = ENV == 0 ? 6 : (ENV == 3 ? 17 : 9);
+  if (lane == 0) {
+#pragma unroll
+    for (int i = 0; i < OD; i++) o[i] = v[i];
+  }
+}
+
+template <int ENV>
+__global__ void __launch_bounds__(32) env_kernel(KParams P) {
+  extern __shared__ __align__(16) unsigned char smraw[];
+  Smem& s = *reinterpret_cast<Smem*>(smraw);
+  const DevModel& M = *P.model;
+  const int env = blockIdx.x, lane = threadIdx.x;
+  constexpr int OD = ENV == 0 ? 6 : (ENV == 3 ? 17 : 9);
+  constexpr int AD = ENV == 3 ? 9 : 3;
+  if (P.mode == MODE_RESET && P.mask && !P.mask[env]) return;
+  float* rec = P.state + (size_t)env * UG_STATE;
+  load_state(s, rec, lane);
+  int step_count = (int)s.st[32], episode = (int)s.st[33];
+  q4 vert = mkq(s.st[34], s.st[35], s.st[36], s.st[37]);
+  float ep_ret = s.st[77];
+  const unsigned gidx = (unsigned)(P.gidx0 + env);
+  const float* dr = P.draws ? P.draws + 4 * env : nullptr;
+  int phase, n = 0, limit = UGP_SETTLE_MAX_TICKS, ticks_step = 0, ticks_reset = 0;
+  long long tick_total = 0;
+  float rew = 0.f; bool term = false, succ = false, trunc = false;
+
+  // ---- what starts the tick loop
+  if (P.mode == MODE_TICKS) { phase = PH_RAW; limit = P.raw_ticks; }
+  else if (P.mode == MODE_RESET) { phase = PH_ARM10; }
+  else {
+    phase = PH_STEP;
+    const float* a = P.action + (size_t)AD * env;
+    fk_bodies(s, M, lane);
+    f3 ep; m3 eR; ee_pose(s, M, ep, eR);
+    if (ENV == 0 || ENV == 1) {          // env_ball_balance_v0.py:112-118
+      if (ENV == 1) rew -= fabsf(a[0]) + fabsf(a[1]) + fabsf(a[2]);
+      f3 e = euler_from_quat(mat_to_quat(eR));
+      move_ee(s, M, ep, quat_from_euler(e.x + a[0], e.y + a[1], e.z + a[2]), lane);
+    } else if (ENV == 2 || ENV == 4) {   // env_cubes_push_v0.py:122-126, env_golf_v0.py:122-126
+      move_ee(s, M, ep + mk3(a[0], a[1], a[2]), vert, lane);
+    } else {                              // env_cubes_grasp_v0.py:121-144
+      float a0 = a[0], a1 = a[1];
+      float u = P.u ? P.u[env] : urand(P.seed, gidx, (unsigned)episode, 16u + (unsigned)step_count);
+      int sel = (a0 + a1 == 0.f) ? (u < 0.5f ? 0 : 1) : (u * (a0 + a1) < a0 ? 0 : 1);
+      if (sel == 0) { float t[6];
+#pragma unroll
+        for (int i = 0; i < 6; i++) t[i] = a[2 + i];
+        set_arm_targets(s, t, lane); }
+      else move_gripper(s, a[8] < 0.5f ? 0.085f : 0.0f, lane);
+    }
+  }
+  // robot.py:85-101: arm to rest pose with zero velocity; task objects removed; episode counters restart
+  auto begin_reset = [&]() {
+    episode++; step_count = 0; ep_ret = 0.f;
+    __syncwarp();
+    if (lane == 0) s.flags &= (FL_ARM | FL_GRIP);
+    if (lane < 6) { s.q[lane] = c_rest_pose[lane]; s.qd[lane] = 0.f; }
+    phase = PH_ARM10; n = 0; limit = UGP_RESET_ARM_TICKS;
+    __syncwarp();
+  };
+  if (phase == PH_ARM10) begin_reset();
+  __syncwarp();
+
+  // ---- the tick loop
+  for (;;) {
+    int iters;
+    float moved = tick(s, M, lane, &iters);
+    n++; tick_total++;
+    bool done = phase == PH_ARM10 || phase == PH_RAW ? n >= limit : (moved < UGP_SETTLE_THRESHOLD || n >= limit);
+    if (!done) continue;
+    if (phase == PH_RAW) break;
+    fk_bodies(s, M, lane);
+    f3 ep; m3 eR; ee_pose(s, M, ep, eR);
+    if (phase == PH_STEP) {
+      ticks_step = n;
+      // ---------------- epilogue: reward / termination
+      if (ENV == 0) {                      // env_ball_balance_v0.py:122-132
+        rew += 1.f; term = s.fpos[1][2] < s.fpos[0][2];
+      } else if (ENV == 1) {               // env_two_balls_balance_v0.py:128-146
+        rew += 1.f;
+#pragma unroll
+        for (int b = 1; b <= 2; b++)
+#pragma unroll
+          for (int k = 0; k < 2; k++) { float x = fabsf(s.fpos[b][k]); rew += x > 1.f ? 0.f : 1.f - x * x; }
+        term = s.fpos[1][2] < s.fpos[0][2] || s.fpos[2][2] < s.fpos[0][2];
+      } else if (ENV == 2) {               // env_cubes_push_v0.py:130-154
+        bool table = touch_robot(s, M, 1, 18, -1, -1);
+        bool fingers = touch_robot(s, M, 9, 18, 2, -1);
+        if (table) rew -= 0.01f;
+        else if (fingers) {
+          float d = norm3(ld3(s.fpos[0]) - ld3(s.fpos[1]));
+          rew = 0.f;
+          if (!P.sparse) rew += geometric_distance_reward(d, 0.1f, 0.5f) / 10.f;
+          if (d < 0.05f) { rew += 10.f; succ = true; }
+          rew += 0.1f; term = succ;
+        }
+        rew -= 0.1f;
+      } else if (ENV == 3) {               // env_cubes_grasp_v0.py:146-173
+        f3 gc = gripper_center(s, M);
+        float d = norm3(gc - ld3(s.fpos[0]));
+        bool grasp_now = touch_robot(s, M, 11, 13, 1, -1) && touch_robot(s, M, 16, 18, 1, -1);
+        int fl = s.flags;
+        __syncwarp();
+        if (!(fl & FL_APPROACHED)) {
+          rew += geometric_distance_reward(d, 0.5f, 2.f) / 4.f;
+          if (d < 0.05f && gripper_opening(s, M) > 0.50f) { fl |= FL_APPROACHED; rew += 5.f; }
+        } else if (!(fl & FL_GRASPED)) {
+          if (grasp_now) { fl |= FL_GRASPED; rew += 5.f; }
+        } else if (grasp_now && s.fpos[0][2] > 0.2f) { rew += 10.f; term = true; succ = true; }
+        if (lane == 0) s.flags = fl;
+        rew -= 0.1f;
+      } else {                             // env_golf_v0.py:130-183
+        f3 hole = mk3(0.f, -0.6f, 0.02f), ball = ld3(s.fpos[1]);
+        bool in_fingers = touch_robot(s, M, 9, 18, 1, -1);
+        if (norm3(hole - ball) < 0.05f) { rew += 10.f; succ = true; term = true; }
+        else if (!in_fingers) { rew -= 5.f; term = true; }
+        else if (ball.z < 0.f) { rew -= 10.f; term = true; }
+        else {
+          bool floor_hit = touch_robot(s, M, 0, 18, -1, 1) || touch_free(s, M, 1, -1, 1);
+          if (floor_hit) rew -= 0.01f;
+          if (!P.sparse) rew += geometric_distance_reward(norm3(club_foot(s) - ball), 0.1f, 0.5f) / 10.f;
+          if (touch_free(s, M, 1, 2, -1)) { rew += 0.1f; if (!P.sparse) rew += geometric_distance_reward(norm3(hole - ball), 0.1f, 0.5f) / 10.f; }
+        }
+        rew -= 0.1f;
+      }
+      __syncwarp();
+      step_count++; ep_ret += rew;
+      trunc = step_count >= M.max_steps;
+      if (P.contacts) {
+        int nc = s.ncon;
+        if (lane < UG_MAXC) { P.contacts[((size_t)env * UG_MAXC + lane) * 2] = lane < nc ? s.con[lane].sa : -1; P.contacts[((size_t)env * UG_MAXC + lane) * 2 + 1] = lane < nc ? s.con[lane].sb : -1; }
+        if (lane == 0) P.ccount[env] = nc;
+      }
+      observe<ENV>(s, M, P.obs + (size_t)OD * env, lane);
+      if (P.final_obs) observe<ENV>(s, M, P.final_obs + (size_t)OD * env, lane);
+      if (lane == 0) { P.reward[env] = rew; P.term[env] = term; P.trunc[env] = trunc; P.succ[env] = succ; }
+      if ((term || trunc) && lane == 0 && P.stats) {
+        atomicAdd(&P.stats[0], 1.0); atomicAdd(&P.stats[1], (double)ep_ret); atomicAdd(&P.stats[2], (double)step_count); atomicAdd(&P.stats[3], succ ? 1.0 : 0.0);
+      }
+      if ((term || trunc) && P.autoreset) { begin_reset(); continue; }
+      break;
+    }
+    ticks_reset += n;
+    if (phase == PH_ARM10) {
+      // ---------------- reset stage 1 (robot.py:100-101 opens the gripper, then the env-specific first move)
+      move_gripper(s, 0.085f, lane);
+      if (ENV == 0 || ENV == 1) {          // env_ball_balance_v0.py:154-158
+        move_ee(s, M, mk3(0.0f, -0.60f, 0.60f), mkq(0.50f, -0.50f, -0.50f, 0.50f), lane);
+        move_gripper(s, 0.085f * 0.2f, lane);
+        phase = PH_SETTLE1;
+      } else if (ENV == 2) {               // env_cubes_push_v0.py:212-227,238-246
+        float d0 = dr ? dr[0] : urand(P.seed, gidx, (unsigned)episode, 0u);
+        f3 c1 = mk3(-0.1f + 0.2f * d0, -0.7f, 0.1f);
+        spawn(s, 0, mk3(0.0f, -0.5f, 0.1f), lane); spawn(s, 1, c1, lane);
+        float sh, ch; sincosf(0.25f * UGP_PI, &sh, &ch);
+        vert = mkq(0.f, sh, 0.f, ch);
+        move_ee(s, M, c1 + mk3(0.f, 0.f, 0.2f), vert, lane);
+        move_gripper(s, 0.0f, lane);
+        phase = PH_SETTLE2;
+      } else if (ENV == 3) {               // env_cubes_grasp_v0.py:276-299,311-327
+        float d0 = dr ? dr[0] : urand(P.seed, gidx, (unsigned)episode, 0u), d1 = dr ? dr[1] : urand(P.seed, gidx, (unsigned)episode, 1u);
+        float r = 0.5f + 0.3f * d0, th = -UGP_PI + UGP_PI * d1, sn, cs; sincosf(th, &sn, &cs);
+        spawn(s, 0, mk3(r * cs, r * sn, 0.1f), lane);
+        move_ee(s, M, ep, link_quat_chain(s.q, M, 7), lane);
+        phase = PH_SETTLE2;
+      } else {                             // env_golf_v0.py:238-256
+        vert = mkq(0.0f, 0.0f, -0.70f, 0.70f);
+        move_ee(s, M, mk3(0.0f, -0.60f, 0.40f), vert, lane);
+        move_gripper(s, 0.085f * 0.2f, lane);
+        phase = PH_SETTLE1;
+      }
+      n = 0; limit = UGP_SETTLE_MAX_TICKS;
+      __syncwarp();
+      continue;
+    }
+    if (phase == PH_SETTLE1) {
+      // ---------------- reset stage 2: spawn the held object and the ball(s), close the gripper
+      f3 gc = gripper_center(s, M);
+      if (ENV == 0 || ENV == 1) {          // env_ball_balance_v0.py:160-168,186-205; env_two_balls_balance_v0.py:200-233
+        f3 pp = mk3(ep.x, ep.y - 0.2f, gc.z);
+        float d0 = dr ? dr[0] : urand(P.seed, gidx, (unsigned)episode, 0u), d1 = dr ? dr[1] : urand(P.seed, gidx, (unsigned)episode, 1u);
+        spawn(s, 0, pp, lane);
+        if (ENV == 0) spawn(s, 1, pp + mk3(-0.03f + 0.06f * d0, -0.08f + 0.10f * d1, 0.2f + 0.02f), lane);
+        else {
+          float d2 = dr ? dr[2] : urand(P.seed, gidx, (unsigned)episode, 2u), d3 = dr ? dr[3] : urand(P.seed, gidx, (unsigned)episode, 3u);
+          spawn(s, 1, pp + mk3(-0.03f + 0.06f * d0, -0.08f + 0.035f * d1, 0.2f + 0.003f), lane);
+          spawn(s, 2, pp + mk3(-0.03f + 0.06f * d2, -0.015f + 0.035f * d3, 0.2f - 0.003f), lane);
+        }
+      } else if (ENV == 4) {               // env_golf_v0.py:258-266,335-340
+        float d0 = dr ? dr[0] : urand(P.seed, gidx, (unsigned)episode, 0u), d1 = dr ? dr[1] : urand(P.seed, gidx, (unsigned)episode, 1u);
+        spawn(s, 0, gc + mk3(0.f, 0.f, -0.05f + (float)UGP_CLUB_ZC), lane);
+        spawn(s, 1, mk3(-0.2f + 0.4f * d0, -0.7f + (-0.1f + 0.2f * d1), 0.1f), lane);
+      }
+      move_gripper(s, 0.0f, lane);
+      phase = PH_SETTLE2; n = 0; limit = UGP_SETTLE_MAX_TICKS;
+      __syncwarp();
+      continue;
+    }
+    // PH_SETTLE2: reset finished -> first observation of the new episode
+    observe<ENV>(s, M, P.obs + (size_t)OD * env, lane);
+    break;
+  }
+  if (P.nticks) {
+    if (P.mode == MODE_STEP) { if (lane == 0) { P.nticks[2 * env] = ticks_step; P.nticks[2 * env + 1] = ticks_reset; } }
+    else if (lane == 0) P.nticks[env] = P.mode == MODE_RESET ? ticks_reset : n;
+  }
+  if (lane == 0 && P.stats) { if (P.mode == MODE_STEP) atomicAdd(&P.stats[4], 1.0); atomicAdd(&P.stats[5], (double)tick_total); }
+  store_state(s, rec, lane, step_count, episode, vert, ep_ret);
+}
+
+// ---- stand-alone kinematics kernels (one thread per query)
+__global__ void fk_kernel(const DevModel* Mp, int n, const float* q, float* pose) {
+  int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  const DevModel& M = *Mp;
+  const float* qi = q + (size_t)UG_NDOF * i;
+  f3 P[UG_NLINK]; q4 Q[UG_NLINK];
+  for (int l = 0; l < UG_NLINK; l++) {
+    int p = M.link_parent[l];
+    f3 pp = p >= 0 ? P[p] : mk3(0, 0, 0); q4 pq = p >= 0 ? Q[p] : mkq(0, 0, 0, 1);
+    P[l] = pp + mulv(quat_to_mat(pq), ld3(M.link_jxyz[l]));
+    q4 r = qmul(pq, mkq(M.link_jquat[l][0], M.link_jquat[l][1], M.link_jquat[l][2], M.link_jquat[l][3]));
+    if (M.link_dof[l] >= 0) r = qmul(r, quat_axis(M.link_axis[l], qi[M.link_dof[l]]));
+    Q[l] = qnormalize(r);
+    float* o = pose + ((size_t)i * UG_NLINK + l) * 7;
+    o[0] = P[l].x; o[1] = P[l].y; o[2] = P[l].z; o[3] = Q[l].x; o[4] = Q[l].y; o[5] = Q[l].z; o[6] = Q[l].w;
+  }
+}
+__global__ void ik_kernel(const DevModel* Mp, int n, const float* q, const float* target, float* out) {
+  int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  const float* t = target + 7 * (size_t)i;
+  float o[6];
+  ik_solve(q + (size_t)UG_NDOF * i, *Mp, mk3(t[0], t[1], t[2]), mkq(t[3], t[4], t[5], t[6]), o);
+  for (int k = 0; k < 6; k++) out[6 * (size_t)i + k] = o[k];
+}
+// one warp per query (reuses the warp-level FK)
+__global__ void __launch_bounds__(32) gripper_center_kernel(const DevModel* Mp, int n, const float* q, float* out) {
+  extern __shared__ __align__(16) unsigned char smraw[];
+  Smem& s = *reinterpret_cast<Smem*>(smraw);
+  int i = blockIdx.x, lane = threadIdx.x;
+  if (lane < UG_NDOF) s.q[lane] = q[(size_t)UG_NDOF * i + lane];
+  if (lane < UG_MAXFREE) { s.fquat[lane][0] = 0; s.fquat[lane][1] = 0; s.fquat[lane][2] = 0; s.fquat[lane][3] = 1; }
+  __syncwarp();
+  fk_bodies(s, *Mp, lane);
+  f3 c = gripper_center(s, *Mp);
+  if (lane == 0) { out[3 * (size_t)i] = c.x; out[3 * (size_t)i + 1] = c.y; out[3 * (size_t)i + 2] = c.z; }
+}

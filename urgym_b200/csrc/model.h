@@ -1,0 +1,43 @@
+// Device-side constant model: the UR5 + Robotiq-85 tree with fixed joints folded into their movable ancestor
+// (12 bodies / 12 DoF), per-sub-link data for Bullet's per-link damping, collision primitives and the pair list.
+// Built once on the host by build_model() from the generated link table (model_data.h, from
+// /root/reference/urgym/urdf/ur5_robotiq_85.urdf via tools/compile_model.py) and uploaded to device memory.
+#pragma once
+#include <stdint.h>
+
+#define UG_NDOF 12
+#define UG_NLINK 19
+#define UG_MAXFREE 3
+#define UG_MAXSHAPES 32
+#define UG_MAXPAIRS 128
+#define UG_MAXC 16
+#define UG_STATE 96
+
+struct DevShape {
+  int kind;    // 0 box, 1 sphere
+  int body;    // 0 robot, 1..3 free body, -1 static
+  int link;    // Bullet link index (robot) or sub-shape id
+  int rbody;   // robot shapes: index of the movable body (dof) that carries the link
+  float lc[3]; float lR[9];  // local centre / rotation in the carrying body's frame (static: world)
+  float half[3]; float radius;
+  float mu, rest, roll, cbt, brad;
+};
+
+struct DevSub { float mass; float com[3]; float I[6]; };  // I: xx xy xz yy yz zz about the sub-link COM, body frame
+
+struct DevModel {
+  int par[UG_NDOF]; uint32_t anc[UG_NDOF]; uint32_t sub[UG_NDOF]; int axis[UG_NDOF];
+  float jpos[UG_NDOF][3]; float jrot[UG_NDOF][9];
+  float mass[UG_NDOF]; float com[UG_NDOF][3]; float I[UG_NDOF][6];
+  int nsub[UG_NDOF]; DevSub subl[UG_NDOF][3];
+  float lower[UG_NDOF], upper[UG_NDOF], effort[UG_NDOF], velocity[UG_NDOF];
+  int link_body[UG_NLINK]; float link_lpos[UG_NLINK][3]; float link_lrot[UG_NLINK][9];
+  float link_jquat[UG_NLINK][4]; float link_jxyz[UG_NLINK][3]; int link_parent[UG_NLINK]; int link_dof[UG_NLINK]; int link_axis[UG_NLINK];
+  float aabb_c[2][3], aabb_h[2][3];  // collision AABBs of links 11 and 16 in their link frames
+  int env_type, nfree, nshapes, npairs, obs_dim, act_dim, max_steps; float gravity;
+  float fmass[UG_MAXFREE]; float finertia[UG_MAXFREE][3];
+  DevShape shapes[UG_MAXSHAPES]; uint8_t pairs[UG_MAXPAIRS][2];
+};
+
+// Host: fills *m for env_type 0..4. Returns 0 or -1.
+int build_model(int env_type, DevModel* m);
