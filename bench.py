@@ -1,0 +1,272 @@
+#!/usr/bin/env python
+"""Headline benchmark: batched URGym env-steps per second on B200 (BASELINE.json metric), one JSON line on stdout.
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--workload ball4096|two16384|push16384|grasp16384|golf16384]
+    python bench.py --impl reference ...     # the CPU arm: the oracle port on the host cores (pybullet is absent)
+
+One "step" is one gym step of every env of the batch: one launch of the fused env kernel (action -> IK -> 1..480
+physics ticks -> reward / termination / observation -> in-kernel auto-reset of finished envs). Actions are synthetic
+random-policy draws from each env's action space. `value` is timed on the device with inputs resident in HBM; `e2e`
+goes through the C ABI's host-buffer entry (urgym_step_host: H2D of the actions, the kernel, D2H of obs / reward /
+flags) and is timed with the host clock around the synchronous calls.
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+WORKLOADS = {  # name -> (env, envs per GPU, BASELINE.json config index)
+    'ball4096': ('BallBalance', 4096, 1),
+    'two16384': ('TwoBallsBalance', 16384, 2),
+    'push16384': ('CubesPush', 16384, 3),
+    'grasp16384': ('CubesGrasp', 16384, 4),
+    'golf16384': ('Golf', 16384, None),
+}
+# algorithmic HBM bytes per env-step (SURVEY.md §8d / DESIGN.md §5): state once in, once out, action in, obs/reward/flags out
+BYTES_PER_ENV_STEP = {'BallBalance': 562, 'TwoBallsBalance': 678, 'CubesPush': 606, 'CubesGrasp': 530, 'Golf': 606}
+METRIC = 'env-steps/sec (batched, device-timed)'
+
+
+def action_sampler(env, n, gen, torch, device):
+    """Random policy over each env's action space (reference spaces, e.g. env_ball_balance_v0.py:52-54)."""
+    if env == 'CubesGrasp':  # env_cubes_grasp_v0.py:74: [0,1]^2 x [-pi,pi]^6 x [0,1]
+        a = torch.rand(n, 9, generator=gen, device=device)
+        a[:, 2:8] = (a[:, 2:8] * 2 - 1) * 3.14159265
+        return a
+    return (torch.rand(n, 3, generator=gen, device=device) * 2 - 1) * 0.1
+
+
+def peaks():
+    p = os.path.join(ROOT, 'MEASURED_PEAKS.json')
+    if os.path.exists(p):
+        with open(p) as f:
+            return float(json.load(f)['hbm_gbs']), 'measured'
+    return 6650.0, 'fallback'
+
+
+class ClockSampler:
+    Q = 'clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap'
+
+    def __init__(self, index):
+        self.rows, self.proc = [], None
+        try:
+            self.proc = subprocess.Popen(['nvidia-smi', '-i', str(index), '--query-gpu=' + self.Q, '--format=csv,noheader,nounits', '-lms', '200'],
+                                         stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.t = threading.Thread(target=self._read, daemon=True)
+            self.t.start()
+        except Exception:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.rows.append(line.strip())
+
+    def stop(self):
+        if not self.proc:
+            return {'sm_mhz': None, 'sm_max_mhz': None, 'reasons': ['nvidia-smi unavailable']}
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=5)
+        except Exception:
+            self.proc.kill()
+        sm, mx, reasons = [], None, set()
+        names = ['hw_slowdown', 'hw_thermal_slowdown', 'sw_thermal_slowdown', 'sw_power_cap']
+        for r in self.rows:
+            f = [x.strip() for x in r.split(',')]
+            if len(f) < 6:
+                continue
+            try:
+                sm.append(float(f[0])); mx = float(f[1])
+            except ValueError:
+                continue
+            for k, nm in enumerate(names):
+                if f[2 + k].lower().startswith('active'):
+                    reasons.add(nm)
+        sm.sort()
+        return {'sm_mhz': sm[len(sm) // 2] if sm else None, 'sm_max_mhz': mx, 'reasons': sorted(reasons), 'samples': len(sm)}
+
+
+def cpu_arm(env, seconds, steps=None, warmup=0, envs_per_thread=4, seed=1234):
+    """The oracle port on the host cores: one thread per core, each stepping its own envs (ctypes releases the GIL).
+
+    If `steps` is given, every thread runs exactly warmup + steps gym steps on its envs and the timed part is the
+    `steps`; otherwise it runs for about `seconds`. Returns (env_steps_per_s, cores, sample description, ms per step).
+    """
+    import numpy as np
+    sys.path.insert(0, os.path.join(ROOT, 'tests'))
+    import oracle_lib as O
+    O.lib()
+    cores = os.cpu_count() or 1
+    res = [None] * cores
+    start_evt = threading.Event()
+
+    def work(t):
+        rng = np.random.default_rng(seed + t)
+        b = O.OracleBatch(env, envs_per_thread, seed=seed, offset=t * envs_per_thread)
+        b.reset()
+
+        def act():
+            if env == 'CubesGrasp':
+                return np.concatenate([rng.uniform(0, 1, (envs_per_thread, 2)), rng.uniform(-np.pi, np.pi, (envs_per_thread, 6)), rng.uniform(0, 1, (envs_per_thread, 1))], 1)
+            return rng.uniform(-0.1, 0.1, (envs_per_thread, b.ad))
+        for _ in range(warmup):
+            b.step(act(), autoreset=True)
+        start_evt.wait()
+        t0 = time.perf_counter(); n = 0
+        while True:
+            b.step(act(), autoreset=True); n += 1
+            if steps is not None:
+                if n >= steps:
+                    break
+            elif time.perf_counter() - t0 > seconds:
+                break
+        res[t] = (n * envs_per_thread, time.perf_counter() - t0, b.total_ticks())
+
+    th = [threading.Thread(target=work, args=(t,)) for t in range(cores)]
+    for x in th:
+        x.start()
+    time.sleep(0.2 if steps is None else 0.0)
+    start_evt.set()
+    for x in th:
+        x.join()
+    total = sum(r[0] for r in res); wall = max(r[1] for r in res)
+    nsteps = steps if steps is not None else None
+    desc = '%s, %d host threads x %d envs, random actions, auto-reset, %s (fp64 C++ restatement; pybullet is not installed on this box)' % (
+        env, cores, envs_per_thread, ('%d gym steps per env' % steps) if steps is not None else ('%.0f s' % seconds))
+    return total / wall, cores, desc, (wall / nsteps * 1e3 if nsteps else None), total
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument('--gpus', type=int, default=1)
+    ap.add_argument('--steps', type=int, default=100)
+    ap.add_argument('--warmup', type=int, default=20)
+    ap.add_argument('--impl', default='b200', choices=['b200', 'reference'])
+    ap.add_argument('--workload', default='ball4096', choices=sorted(WORKLOADS))
+    ap.add_argument('--envs', type=int, default=0, help='override envs per GPU')
+    ap.add_argument('--cpu-seconds', type=float, default=12.0)
+    ap.add_argument('--no-cpu', action='store_true')
+    ap.add_argument('--no-e2e', action='store_true')
+    args = ap.parse_args()
+    env, n_envs, cfg_idx = WORKLOADS[args.workload]
+    if args.envs:
+        n_envs = args.envs
+    rank = int(os.environ.get('RANK', '0')); world = int(os.environ.get('WORLD_SIZE', '1')); local = int(os.environ.get('LOCAL_RANK', '0'))
+    config = {'workload': 'URGym/%s-v0 batched %d envs per GPU, random policy, in-kernel auto-reset' % (env, n_envs),
+              'baseline_config_index': cfg_idx, 'envs_per_gpu': n_envs, 'l2': 'L2 flushed (256 MiB write) between timed steps'}
+
+    if args.impl == 'reference':
+        if rank != 0:
+            return
+        v, cores, desc, ms, total = cpu_arm(env, None, steps=args.steps, warmup=args.warmup)
+        line = {'impl': 'reference', 'metric': METRIC, 'value': v, 'unit': 'env-steps/s', 'n_gpus': args.gpus, 'steps': args.steps, 'warmup': args.warmup,
+                'ms_per_step': ms, 'higher_is_better': True, 'scaling': 'weak', 'vs_baseline': None, 'dtype': 'f64', 'data': 'synthetic',
+                'config': config, 'cpu_baseline': {'value': v, 'unit': 'env-steps/s', 'cores': cores, 'kind': 'port', 'sample': desc},
+                'e2e': {'value': v, 'unit': 'env-steps/s', 'h2d_bytes_per_step': 0, 'd2h_bytes_per_step': 0}, 'gpu_launches': 0}
+        print(json.dumps(line)); return
+
+    import torch
+    import torch.distributed as dist
+    from urgym_b200 import _lib
+    from urgym_b200.batch import EnvBatch
+    if not torch.cuda.is_available():
+        raise SystemExit('bench.py: no CUDA device; urgym_b200 has no CPU path (use --impl reference for the CPU arm)')
+    torch.cuda.set_device(local)
+    dev = torch.device('cuda', local)
+    if world > 1:
+        dist.init_process_group('nccl', device_id=dev)
+
+    def barrier():
+        if world > 1:
+            dist.barrier(device_ids=[local])
+        torch.cuda.synchronize(dev)
+
+    b = EnvBatch(env, n_envs, device=local, seed=20261104, env_index_offset=rank * n_envs)
+    gen = torch.Generator(device=dev); gen.manual_seed(1000 + rank)
+    K, W = args.steps, args.warmup
+    actions = [action_sampler(env, n_envs, gen, torch, dev) for _ in range(K + W)]
+    flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)
+    b.reset()
+    for i in range(W):
+        b.step(actions[i]); flush.fill_(i & 255)
+    barrier()
+    st0 = b.stats(); l0 = _lib.lib().urgym_launch_count()
+    clocks = ClockSampler(local) if rank == 0 else None
+    ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(K)]
+    barrier()
+    for i in range(K):
+        ev[i][0].record()
+        b.step(actions[W + i])
+        ev[i][1].record()
+        flush.fill_(i & 255)
+    barrier()
+    l1 = _lib.lib().urgym_launch_count(); st1 = b.stats()
+    ms_total = sum(a.elapsed_time(c) for a, c in ev)
+    clk = clocks.stop() if clocks else None
+    t = torch.tensor([ms_total], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    ms_total = float(t.item())
+    value = world * n_envs * K / (ms_total * 1e-3)
+    ticks = st1['ticks'] - st0['ticks']; esteps = st1['env_steps'] - st0['env_steps']
+
+    # ---- e2e: host buffers through urgym_step_host (pinned), H2D + kernel + D2H inside the timed region
+    e2e = None
+    if not args.no_e2e:
+        import ctypes as C
+        L = _lib.lib(); od, ad = b.obs_dim, b.act_dim
+        h_act = [a.cpu().pin_memory() for a in actions[:min(len(actions), 8)]]
+        h_obs = torch.empty(n_envs, od).pin_memory(); h_rew = torch.empty(n_envs).pin_memory()
+        h_term = torch.empty(n_envs, dtype=torch.uint8).pin_memory(); h_trunc = torch.empty(n_envs, dtype=torch.uint8).pin_memory(); h_succ = torch.empty(n_envs, dtype=torch.uint8).pin_memory()
+        p = lambda x: C.c_void_p(x.data_ptr())
+        Ke = max(3, K // 4)
+
+        def estep(i):
+            _lib.check(L.urgym_step_host(b.h, p(h_act[i % len(h_act)]), None, None, p(h_obs), p(h_rew), p(h_term), p(h_trunc), p(h_succ), None, None, 1))
+        for i in range(3):
+            estep(i)
+        barrier()
+        t0 = time.perf_counter()
+        for i in range(Ke):
+            estep(i)
+        torch.cuda.synchronize(dev)
+        dt = time.perf_counter() - t0
+        t = torch.tensor([dt], dtype=torch.float64, device=dev)
+        if world > 1:
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        e2e = {'value': world * n_envs * Ke / float(t.item()), 'unit': 'env-steps/s', 'h2d_bytes_per_step': n_envs * ad * 4,
+               'd2h_bytes_per_step': n_envs * (od * 4 + 4 + 3), 'steps': Ke, 'timer': 'host clock around synchronous urgym_step_host calls'}
+
+    gstats = torch.tensor([ticks, esteps], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(gstats)
+    if rank == 0:
+        peak, how = peaks()
+        ms_step = ms_total / K
+        achieved = BYTES_PER_ENV_STEP[env] * n_envs / (ms_step * 1e-3) / 1e9
+        line = {'metric': METRIC, 'value': value, 'unit': 'env-steps/s', 'n_gpus': world, 'steps': K, 'warmup': W, 'ms_per_step': ms_step,
+                'higher_is_better': True, 'scaling': 'weak', 'vs_baseline': None, 'dtype': 'f32', 'data': 'synthetic', 'config': config,
+                'ticks_per_env_step': float(gstats[0].item() / max(gstats[1].item(), 1)), 'physics_ticks_per_s': float(gstats[0].item() / (ms_total * 1e-3)),
+                'gpu_launches': int(l1 - l0), 'clocks': clk,
+                'roofline': {'bound': 'hbm', 'achieved': achieved, 'peak': peak, 'unit': 'GB/s', 'frac': achieved / peak, 'traffic': None,
+                             'peak_source': how, 'kernel': 'env_kernel<%s>' % env,
+                             'note': 'latency/issue-bound fused tick loop; see profiles/ for SM issue utilisation'}}
+        if e2e:
+            line['e2e'] = e2e
+        if world == 1 and not args.no_cpu:
+            v, cores, desc, _, _ = cpu_arm(env, args.cpu_seconds)
+            line['cpu_baseline'] = {'value': v, 'unit': 'env-steps/s', 'cores': cores, 'kind': 'port', 'sample': desc}
+        print(json.dumps(line), flush=True)
+    b.close()
+    if world > 1:
+        dist.destroy_process_group()
+
+
+if __name__ == '__main__':
+    main()

@@ -369,6 +369,11 @@ int urgo_last_contacts_detail(void* h, int env, double* out /*[MAXC][11]: sa, sb
   }
   return n;
 }
+// summed profiling counters over all envs: ticks, solver iterations, rows, contacts, rows*iterations
+void urgo_tick_stats(void* h, long* out5) {
+  for (int k = 0; k < 5; k++) out5[k] = 0;
+  for (auto& e : ((Batch*)h)->envs) { out5[0] += e.w.st_ticks; out5[1] += e.w.st_iters; out5[2] += e.w.st_rows; out5[3] += e.w.st_contacts; out5[4] += e.w.st_rowiters; }
+}
 int urgo_last_iters(void* h, int env) { return ((Batch*)h)->envs[env].w.last_iters; }
 // link frames for joint vector q[12]: out[19][7] = pos xyz, quat xyzw (getLinkState(...)[4], [5])
 void urgo_fk(const double* q, double* out) {
