@@ -23,6 +23,7 @@ sys.path.insert(0, ROOT)
 
 WORKLOADS = {  # name -> (env, envs per GPU, BASELINE.json config index)
     'ball4096': ('BallBalance', 4096, 1),
+    'ball16384': ('BallBalance', 16384, None),
     'two16384': ('TwoBallsBalance', 16384, 2),
     'push16384': ('CubesPush', 16384, 3),
     'grasp16384': ('CubesGrasp', 16384, 4),

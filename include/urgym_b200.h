@@ -93,6 +93,11 @@ int urgym_gripper_center(int device, int n, const float* q_dev, float* out_dev, 
 /* Episode statistics accumulated on device since creation: {episodes, return sum, length sum, successes, env steps,
  * physics ticks}. Synchronises the handle's last stream. (Optional NCCL reduction happens in the Python host.) */
 int urgym_stats(urgym_handle h, double out[6]);
+/* Launch geometry of the fused env kernel: lanes of a warp that run one env, and shared-memory bytes per env. */
+int urgym_kernel_info(int env_type, int* group_lanes, int* smem_bytes_per_env);
+/* Development aid: per-phase warp cycles of the tick (fk, collide, dynamics, row setup, T build, sweeps, integrate)
+ * accumulated since the last call; returns URGYM_E_STATE unless the library was built with -DUG_PHASE_TIMING. */
+int urgym_phase_cycles(unsigned long long out[8]);
 /* Kernel launches issued by this library in this process (bench.py's gpu_launches claim). */
 long long urgym_launch_count(void);
 const char* urgym_last_error(void);

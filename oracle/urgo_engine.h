@@ -290,6 +290,7 @@ struct World {
   std::vector<Contact> contacts;
   int last_iters = 0;
   long st_ticks = 0, st_iters = 0, st_rows = 0, st_contacts = 0, st_rowiters = 0;  // profiling counters (tests / design notes)
+  long st_hist_rows[96] = {0}, st_hist_nc[24] = {0}, st_hist_nnc[32] = {0};
 
   explicit World(int env_type) : sc(make_scene(env_type)) { for (int i = 0; i < NMOTOR; i++) target[i] = 0; }
 
@@ -501,7 +502,7 @@ struct World {
       if (res <= BP_RESIDUAL_THRESHOLD) { it++; break; }
     }
     last_iters = it;
-    { long R = (long)(nc.size() + nr.size() + tr.size() + fr.size()); st_ticks++; st_iters += it; st_rows += R; st_contacts += (long)contacts.size(); st_rowiters += R * it; }
+    { long R = (long)(nc.size() + nr.size() + tr.size() + fr.size()); st_ticks++; st_iters += it; st_rows += R; st_contacts += (long)contacts.size(); st_rowiters += R * it; st_hist_rows[R < 95 ? R : 95]++; st_hist_nc[contacts.size() < 23 ? contacts.size() : 23]++; st_hist_nnc[nc.size() < 31 ? nc.size() : 31]++; }
     // --- apply and integrate (semi-implicit Euler; exponential map for free-body orientation)
     for (int d = 0; d < NDOF; d++) {
       rob.qd[d] = std::fmax(-BP_MAX_COORD_VEL, std::fmin(BP_MAX_COORD_VEL, rob.qd[d] + dv.r[d]));

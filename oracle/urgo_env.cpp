@@ -374,6 +374,10 @@ void urgo_tick_stats(void* h, long* out5) {
   for (int k = 0; k < 5; k++) out5[k] = 0;
   for (auto& e : ((Batch*)h)->envs) { out5[0] += e.w.st_ticks; out5[1] += e.w.st_iters; out5[2] += e.w.st_rows; out5[3] += e.w.st_contacts; out5[4] += e.w.st_rowiters; }
 }
+void urgo_tick_hist(void* h, long* rows96, long* nc24, long* nnc32) {
+  for (int k = 0; k < 96; k++) rows96[k] = 0; for (int k = 0; k < 24; k++) nc24[k] = 0; for (int k = 0; k < 32; k++) nnc32[k] = 0;
+  for (auto& e : ((Batch*)h)->envs) { for (int k = 0; k < 96; k++) rows96[k] += e.w.st_hist_rows[k]; for (int k = 0; k < 24; k++) nc24[k] += e.w.st_hist_nc[k]; for (int k = 0; k < 32; k++) nnc32[k] += e.w.st_hist_nnc[k]; }
+}
 int urgo_last_iters(void* h, int env) { return ((Batch*)h)->envs[env].w.last_iters; }
 // link frames for joint vector q[12]: out[19][7] = pos xyz, quat xyzw (getLinkState(...)[4], [5])
 void urgo_fk(const double* q, double* out) {

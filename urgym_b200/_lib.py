@@ -45,6 +45,7 @@ def lib():
     L.urgym_gripper_center.argtypes = [i32, i32, vp, vp, vp]
     L.urgym_stats.argtypes = [vp, C.POINTER(C.c_double)]
     L.urgym_shape_info.argtypes = [i32, i32, C.POINTER(i32), C.POINTER(i32)]
+    L.urgym_kernel_info.argtypes = [i32, C.POINTER(i32), C.POINTER(i32)]
     L.urgym_launch_count.restype = C.c_longlong
     L.urgym_last_error.restype = C.c_char_p
     _lib = L

@@ -28,6 +28,7 @@ def build(force=False, verbose=False):
            '-Xcompiler', '-fPIC', '-shared', '-o', SO] + SRC
     if verbose:
         cmd += ['-Xptxas', '-v']
+    cmd += os.environ.get('URGYM_NVCC_FLAGS', '').split()
     subprocess.check_call(cmd)
     return SO
 

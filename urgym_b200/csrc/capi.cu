@@ -8,6 +8,9 @@
 #include <vector>
 
 #include "../../include/urgym_b200.h"
+#ifndef UG_DEFAULT_GROUP
+#define UG_DEFAULT_GROUP 32
+#endif
 #include "kernels.cuh"
 
 namespace {
@@ -39,20 +42,33 @@ struct urgym_env_s {
 
 namespace {
 
-template <int ENV>
-int launch_env(urgym_handle h, const KParams& P, cudaStream_t st) {
+// G lanes of a warp run one env. URGYM_GROUP=32 selects the warp-per-env variant (for comparison runs).
+int group_size() {
+  static int g = 0;
+  if (!g) { const char* e = getenv("URGYM_GROUP"); g = (e && atoi(e) == 32) ? 32 : (e && atoi(e) == 16 ? 16 : UG_DEFAULT_GROUP); }
+  return g;
+}
+
+template <int ENV, int G>
+int launch_env_g(urgym_handle h, const KParams& P, cudaStream_t st) {
   static bool attr_done[16] = {false};
-  size_t smem = sizeof(Smem);
+  constexpr int EPB = 32 / G;  // envs per 32-thread block
+  size_t smem = sizeof(SmemT<EnvRC<ENV>::value>) * EPB;
+  if (getenv("URGYM_EXTRA_SMEM")) smem += (size_t)atoi(getenv("URGYM_EXTRA_SMEM"));  // occupancy experiments only
   if (!attr_done[h->device & 15]) {
-    CK(cudaFuncSetAttribute(env_kernel<ENV>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    CK(cudaFuncSetAttribute(env_kernel<ENV>, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared));
+    CK(cudaFuncSetAttribute(env_kernel<ENV, G>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    CK(cudaFuncSetAttribute(env_kernel<ENV, G>, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared));
     attr_done[h->device & 15] = true;
   }
-  env_kernel<ENV><<<h->N, 32, smem, st>>>(P);
+  env_kernel<ENV, G><<<(h->N + EPB - 1) / EPB, 32, smem, st>>>(P);
   g_launches++;
   CK(cudaGetLastError());
   h->last_stream = st;
   return URGYM_OK;
+}
+template <int ENV>
+int launch_env(urgym_handle h, const KParams& P, cudaStream_t st) {
+  return group_size() == 32 ? launch_env_g<ENV, 32>(h, P, st) : launch_env_g<ENV, 16>(h, P, st);
 }
 
 int launch(urgym_handle h, KParams& P, void* stream) {
@@ -238,8 +254,8 @@ int urgym_ik(int device, int n, const float* q_dev, const float* target_dev, flo
 int urgym_gripper_center(int device, int n, const float* q_dev, float* out_dev, void* stream) {
   if (n <= 0 || !q_dev || !out_dev) return fail(URGYM_E_ARG, "urgym_gripper_center: bad arguments");
   DevModel* dm; int rc = kin_model(device, &dm); if (rc) return rc;
-  CK(cudaFuncSetAttribute(gripper_center_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(Smem)));
-  gripper_center_kernel<<<n, 32, sizeof(Smem), (cudaStream_t)stream>>>(dm, n, q_dev, out_dev); g_launches++;
+  CK(cudaFuncSetAttribute(gripper_center_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(SmemKin)));
+  gripper_center_kernel<<<n, 32, sizeof(SmemKin), (cudaStream_t)stream>>>(dm, n, q_dev, out_dev); g_launches++;
   CK(cudaGetLastError()); return URGYM_OK;
 }
 
@@ -249,6 +265,25 @@ int urgym_stats(urgym_handle h, double out[6]) {
   if (h->last_stream) CK(cudaStreamSynchronize(h->last_stream));
   CK(cudaMemcpy(out, h->stats, 6 * sizeof(double), cudaMemcpyDeviceToHost));
   return URGYM_OK;
+}
+int urgym_kernel_info(int env_type, int* group_lanes, int* smem_bytes_per_env) {
+  if (env_type < 0 || env_type > 4 || !group_lanes || !smem_bytes_per_env) return fail(URGYM_E_ARG, "urgym_kernel_info: bad arguments");
+  *group_lanes = group_size();
+  *smem_bytes_per_env = env_type == 4 ? (int)sizeof(SmemT<EnvRC<4>::value>) : (int)sizeof(SmemT<EnvRC<0>::value>);
+  return URGYM_OK;
+}
+// Development aid (only meaningful in a -DUG_PHASE_TIMING build): summed per-phase warp cycles since the last call.
+int urgym_phase_cycles(unsigned long long out[8]) {
+#ifdef UG_PHASE_TIMING
+  CK(cudaDeviceSynchronize());
+  CK(cudaMemcpyFromSymbol(out, g_phase_cycles, 8 * sizeof(unsigned long long)));
+  unsigned long long z[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+  CK(cudaMemcpyToSymbol(g_phase_cycles, z, sizeof(z)));
+  return URGYM_OK;
+#else
+  for (int i = 0; i < 8; i++) out[i] = 0;
+  return URGYM_E_STATE;
+#endif
 }
 long long urgym_launch_count(void) { return g_launches.load(); }
 const char* urgym_last_error(void) { return g_err.c_str(); }

@@ -32,7 +32,8 @@ UG_DEV float geometric_distance_reward(float v, float ts, float tmax) {         
 }
 
 // World pose of ee_link (Bullet link 7) from the body that carries it (robot.py:142-145).
-UG_DEV void ee_pose(const Smem& s, const DevModel& M, f3& p, m3& R) {
+template <class S>
+UG_DEV void ee_pose(const S& s, const DevModel& M, f3& p, m3& R) {
   int b = M.link_body[7];
   m3 Rb = ldm(s.bR[b]);
   p = ld3(s.bp[b]) + mulv(Rb, ld3(M.link_lpos[7]));
@@ -142,7 +143,8 @@ __device__ __noinline__ void ik_solve(const float* q_in, const DevModel& M, f3 t
 }
 
 // Midpoint of the union of the world AABBs of links 11 and 16 (env_ball_balance_v0.py:249-275). Needs fresh FK.
-UG_DEV f3 gripper_center(const Smem& s, const DevModel& M) {
+template <class S>
+UG_DEV f3 gripper_center(const S& s, const DevModel& M) {
   f3 lo = mk3(1e30f, 1e30f, 1e30f), hi = mk3(-1e30f, -1e30f, -1e30f);
 #pragma unroll
   for (int t = 0; t < 2; t++) {
@@ -157,76 +159,93 @@ UG_DEV f3 gripper_center(const Smem& s, const DevModel& M) {
   }
   return (lo + hi) * 0.5f;
 }
-UG_DEV float gripper_opening(const Smem& s, const DevModel& M) {  // env_cubes_grasp_v0.py:340-377
+template <class S>
+UG_DEV float gripper_opening(const S& s, const DevModel& M) {  // env_cubes_grasp_v0.py:340-377
   float v = norm3(ld3(s.bp[M.link_body[16]]) - ld3(s.bp[M.link_body[11]])) - 0.052f;
   return fminf(fmaxf(v, 0.f), 0.085f) / 0.085f;
 }
 
-UG_DEV void load_state(Smem& s, const float* rec, int lane) {
-  for (int i = lane; i < UG_STATE; i += 32) s.st[i] = rec[i];
-  __syncwarp();
-  if (lane < UG_NDOF) { s.q[lane] = s.st[lane]; s.qd[lane] = s.st[12 + lane]; }
-  if (lane < 7) s.tgt[lane] = s.st[24 + lane];
-  if (lane == 0) s.flags = (int)s.st[31];
+template <int G, class S>
+UG_DEV void load_state(S& s, const float* rec, const Gp<G>& gp) {
+  const int lane = gp.l;
+  float* st = s.u.st;
+  for (int i = lane; i < UG_STATE; i += G) st[i] = rec[i];
+  gp.sync();
+  if (lane < UG_NDOF) { s.q[lane] = st[lane]; s.qd[lane] = st[12 + lane]; }
+  if (lane < 7) s.tgt[lane] = st[24 + lane];
+  if (lane == 0) s.flags = (int)st[31];
   if (lane < UG_MAXFREE) {
-    const float* p = s.st + 38 + 13 * lane;
+    const float* p = st + 38 + 13 * lane;
     st3(s.fpos[lane], ld3(p)); s.fquat[lane][0] = p[3]; s.fquat[lane][1] = p[4]; s.fquat[lane][2] = p[5]; s.fquat[lane][3] = p[6];
     st3(s.flin[lane], ld3(p + 7)); st3(s.fang[lane], ld3(p + 10));
   }
-  __syncwarp();
+  gp.sync();
 }
-UG_DEV void store_state(Smem& s, float* rec, int lane, int step_count, int episode, q4 vert, float ep_ret) {
-  __syncwarp();
-  if (lane < UG_NDOF) { s.st[lane] = s.q[lane]; s.st[12 + lane] = s.qd[lane]; }
-  if (lane < 7) s.st[24 + lane] = s.tgt[lane];
-  if (lane == 0) { s.st[31] = (float)s.flags; s.st[32] = (float)step_count; s.st[33] = (float)episode; s.st[34] = vert.x; s.st[35] = vert.y; s.st[36] = vert.z; s.st[37] = vert.w; s.st[77] = ep_ret; }
+// The record's unused slots (78..95) are rewritten as zeros; slot 77 carries the running episode return.
+template <int G, class S>
+UG_DEV void store_state(S& s, float* rec, const Gp<G>& gp, int step_count, int episode, q4 vert, float ep_ret) {
+  const int lane = gp.l;
+  float* st = s.u.st;
+  gp.sync();
+  for (int i = lane; i < UG_STATE; i += G) st[i] = 0.f;
+  gp.sync();
+  if (lane < UG_NDOF) { st[lane] = s.q[lane]; st[12 + lane] = s.qd[lane]; }
+  if (lane < 7) st[24 + lane] = s.tgt[lane];
+  if (lane == 0) { st[31] = (float)s.flags; st[32] = (float)step_count; st[33] = (float)episode; st[34] = vert.x; st[35] = vert.y; st[36] = vert.z; st[37] = vert.w; st[77] = ep_ret; }
   if (lane < UG_MAXFREE) {
-    float* p = s.st + 38 + 13 * lane;
+    float* p = st + 38 + 13 * lane;
     st3(p, ld3(s.fpos[lane])); p[3] = s.fquat[lane][0]; p[4] = s.fquat[lane][1]; p[5] = s.fquat[lane][2]; p[6] = s.fquat[lane][3];
     st3(p + 7, ld3(s.flin[lane])); st3(p + 10, ld3(s.fang[lane]));
   }
-  __syncwarp();
-  for (int i = lane; i < UG_STATE; i += 32) rec[i] = s.st[i];
+  gp.sync();
+  for (int i = lane; i < UG_STATE; i += G) rec[i] = st[i];
 }
 
-UG_DEV void spawn(Smem& s, int b, f3 pos, int lane) {
+template <class S>
+UG_DEV void spawn(S& s, int b, f3 pos, int lane) {
   if (lane == 0) {
     st3(s.fpos[b], pos); s.fquat[b][0] = 0.f; s.fquat[b][1] = 0.f; s.fquat[b][2] = 0.f; s.fquat[b][3] = 1.f;
     st3(s.flin[b], mk3(0, 0, 0)); st3(s.fang[b], mk3(0, 0, 0)); s.flags |= FL_BODY0 << b;
   }
 }
-UG_DEV void set_arm_targets(Smem& s, const float* t, int lane) {
+template <class S>
+UG_DEV void set_arm_targets(S& s, const float* t, int lane) {
   if (lane == 0) {
 #pragma unroll
     for (int i = 0; i < 6; i++) s.tgt[i] = t[i];
     s.flags |= FL_ARM;
   }
 }
-UG_DEV void move_ee(Smem& s, const DevModel& M, f3 pos, q4 quat, int lane) {
+template <int G, class S>
+UG_DEV void move_ee(S& s, const DevModel& M, f3 pos, q4 quat, const Gp<G>& gp) {
   float t[6]; ik_solve(s.q, M, pos, quat, t);
-  __syncwarp();
-  set_arm_targets(s, t, lane);
+  gp.sync();
+  set_arm_targets(s, t, gp.l);
 }
-UG_DEV void move_gripper(Smem& s, float len, int lane) { if (lane == 0) { s.tgt[6] = gripper_angle(len); s.flags |= FL_GRIP; } }
+template <class S>
+UG_DEV void move_gripper(S& s, float len, int lane) { if (lane == 0) { s.tgt[6] = gripper_angle(len); s.flags |= FL_GRIP; } }
 
 // any contact of the last tick matching (body of A == 0 robot with link in [l0,l1]) x (B.body == bb, optional B.link)
-UG_DEV bool touch_robot(const Smem& s, const DevModel& M, int l0, int l1, int bb, int blink) {
+template <class S>
+UG_DEV bool touch_robot(const S& s, const DevModel& M, int l0, int l1, int bb, int blink) {
   bool hit = false;
   for (int i = 0; i < s.ncon; i++) {
-    const DevShape& A = M.shapes[s.con[i].sa]; const DevShape& B = M.shapes[s.con[i].sb];
+    const DevShape& A = M.shapes[s.con[i].shapes & 255]; const DevShape& B = M.shapes[s.con[i].shapes >> 8];
     if (A.body == 0 && A.link >= l0 && A.link <= l1 && (bb < 0 ? B.body < 0 : B.body == bb) && (blink < 0 || B.link == blink)) hit = true;
   }
   return hit;
 }
-UG_DEV bool touch_free(const Smem& s, const DevModel& M, int ba, int bb, int blink) {
+template <class S>
+UG_DEV bool touch_free(const S& s, const DevModel& M, int ba, int bb, int blink) {
   bool hit = false;
   for (int i = 0; i < s.ncon; i++) {
-    const DevShape& A = M.shapes[s.con[i].sa]; const DevShape& B = M.shapes[s.con[i].sb];
+    const DevShape& A = M.shapes[s.con[i].shapes & 255]; const DevShape& B = M.shapes[s.con[i].shapes >> 8];
     if (A.body == ba && (bb < 0 ? B.body < 0 : B.body == bb) && (blink < 0 || B.link == blink)) hit = true;
   }
   return hit;
 }
-UG_DEV f3 club_foot(const Smem& s) {  // env_golf_v0.py:368-373: COM of the club's link 0 (the transversal part)
+template <class S>
+UG_DEV f3 club_foot(const S& s) {  // env_golf_v0.py:368-373: COM of the club's link 0 (the transversal part)
   m3 R = quat_to_mat(mkq(s.fquat[0][0], s.fquat[0][1], s.fquat[0][2], s.fquat[0][3]));
   return ld3(s.fpos[0]) + mulv(R, mk3(0.f, 0.f, (float)(-0.09 - UGP_CLUB_ZC)));
 }

@@ -89,13 +89,35 @@ UG_DEV void plane_space(f3 n, f3& p, f3& q) {
   if (fabsf(n.z) > 0.7071067811865475244f) { float a = n.y * n.y + n.z * n.z, k = rsqrtf(a); p = mk3(0.f, -n.z * k, n.y * k); q = mk3(a * k, -n.x * p.z, n.x * p.y); }
   else { float a = n.x * n.x + n.y * n.y, k = rsqrtf(a); p = mk3(-n.y * k, n.x * k, 0.f); q = mk3(-n.z * p.y, n.z * p.x, a * k); }
 }
-UG_DEV float warp_sum(float v) {
+// 32-bit shared-memory addressing for the solver's hot loops (one IADD + LDS per operand, no generic-address math)
+UG_DEV unsigned smem_u32(const void* p) { return (unsigned)__cvta_generic_to_shared(p); }
+UG_DEV float lds(unsigned a) { float v; asm("ld.shared.f32 %0, [%1];" : "=f"(v) : "r"(a)); return v; }
+// ---- lane groups: G consecutive lanes of a warp run one env (G = 32: warp per env; G = 16: two envs per warp).
+// All intra-env communication goes through these helpers, so the two halves of a warp never wait for each other.
+template <int G>
+struct Gp {
+  int l;          // lane within the group
+  unsigned mask;  // lanes of this group within the warp
+  int shift;      // first lane of the group within the warp
+  __device__ __forceinline__ void sync() const { __syncwarp(mask); }
+  __device__ __forceinline__ float shfl(float v, int src) const { return __shfl_sync(mask, v, src, G); }
+  __device__ __forceinline__ int shfl(int v, int src) const { return __shfl_sync(mask, v, src, G); }
+  __device__ __forceinline__ unsigned ballot(bool p) const { return (__ballot_sync(mask, p) >> shift) & (G == 32 ? 0xffffffffu : ((1u << (G & 31)) - 1u)); }
+  __device__ __forceinline__ float sum(float v) const {
 #pragma unroll
-  for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
-  return v;
-}
-UG_DEV float warp_max(float v) {
+    for (int o = G / 2; o > 0; o >>= 1) v += __shfl_xor_sync(mask, v, o, G);
+    return v;
+  }
+  __device__ __forceinline__ float max(float v) const {
 #pragma unroll
-  for (int o = 16; o > 0; o >>= 1) v = fmaxf(v, __shfl_xor_sync(0xffffffffu, v, o));
-  return v;
+    for (int o = G / 2; o > 0; o >>= 1) v = fmaxf(v, __shfl_xor_sync(mask, v, o, G));
+    return v;
+  }
+};
+template <int G>
+__device__ __forceinline__ Gp<G> make_gp() {
+  Gp<G> g; const int lane = threadIdx.x & 31;
+  g.l = lane & (G - 1); g.shift = lane & ~(G - 1);
+  g.mask = G == 32 ? 0xffffffffu : (((1u << (G & 31)) - 1u) << g.shift);
+  return g;
 }

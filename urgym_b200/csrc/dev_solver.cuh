@@ -1,20 +1,43 @@
-// Collision -> solver rows -> contact-space projected Gauss-Seidel -> integration, for one env per warp.
+// Collision -> solver rows -> projected Gauss-Seidel -> integration, for one env per lane group.
+//
+// Solver layout. Rows keep the oracle's order: joint rows (active limits by DoF, arm motors, gripper
+// motor, five gears), then per sweep normals, rolling-friction rows, friction pairs. Every joint row is a bound on
+// the velocity along one of 17 "extended joint columns" (12 unit DoFs + 5 gear combinations), so its response to any
+// impulse is one entry of E; contact rows respond to each other through the packed triangle T. Lane l owns joint row
+// l (+G ...) and contact rows l, l+G, ...: per row it keeps w = J.dv and the applied impulse in registers, so one
+// Gauss-Seidel step is: owner clamps, one shuffle broadcasts the impulse change, every lane does one FMA per row it
+// owns with an operand read from shared memory.
 #pragma once
 #include "dev_engine.cuh"
 
-UG_DEV void shape_box(const Smem& s, const DevShape& S, BoxW& b) {
-  m3 lR = ldm(S.lR); f3 lc = ld3(S.lc);
-  if (S.body == 0) { m3 R = ldm(s.bR[S.rbody]); b.R = mulm(R, lR); b.c = ld3(s.bp[S.rbody]) + mulv(R, lc); }
-  else if (S.body > 0) { m3 R = ldm(s.fR[S.body - 1]); b.R = mulm(R, lR); b.c = ld3(s.fpos[S.body - 1]) + mulv(R, lc); }
+// Optional per-phase cycle accounting (build with -DUG_PHASE_TIMING; tools/phase_timing.py). Phases: 0 fk, 1 collide,
+// 2 dynamics, 3 row setup + pass 1, 4 T build, 5 Gauss-Seidel sweeps, 6 velocity update + integration.
+#ifdef UG_PHASE_TIMING
+__device__ unsigned long long g_phase_cycles[8];
+#define UG_T0() long long t_ph_ = clock64()
+#define UG_TP(i) { long long t2_ = clock64(); if ((threadIdx.x & 31) == 0) atomicAdd(&g_phase_cycles[i], (unsigned long long)(t2_ - t_ph_)); t_ph_ = t2_; }
+#else
+#define UG_T0()
+#define UG_TP(i)
+#endif
+
+template <class S>
+UG_DEV void shape_box(const S& s, const DevShape& Sh, BoxW& b) {
+  m3 lR = ldm(Sh.lR); f3 lc = ld3(Sh.lc);
+  if (Sh.body == 0) { m3 R = ldm(s.bR[Sh.rbody]); b.R = mulm(R, lR); b.c = ld3(s.bp[Sh.rbody]) + mulv(R, lc); }
+  else if (Sh.body > 0) { m3 R = ldm(s.fR[Sh.body - 1]); b.R = mulm(R, lR); b.c = ld3(s.fpos[Sh.body - 1]) + mulv(R, lc); }
   else { b.R = lR; b.c = lc; }
-  b.h = ld3(S.half);
+  b.h = ld3(Sh.half);
 }
 
 // Lane per candidate pair; manifold points are appended in pair order and capped at UG_MAXC.
-__device__ __noinline__ void collide(Smem& s, const DevModel& M, int lane) {
+template <int G, class S>
+__device__ __noinline__ void collide(S& s, const DevModel& M, const Gp<G> gp) {
+  const int l = gp.l;
   int base = 0;
-  for (int p0 = 0; p0 < M.npairs && base < UG_MAXC; p0 += 32) {
-    int p = p0 + lane, n = 0, sa = 0, sb = 0;
+#pragma unroll 1
+  for (int p0 = 0; p0 < M.npairs && base < UG_MAXC; p0 += G) {
+    int p = p0 + l, n = 0, sa = 0, sb = 0;
     CPt pts[4];
     if (p < M.npairs) {
       sa = M.pairs[p][0]; sb = M.pairs[p][1];
@@ -50,289 +73,434 @@ __device__ __noinline__ void collide(Smem& s, const DevModel& M, int lane) {
     }
     int incl = n;
 #pragma unroll
-    for (int o = 1; o < 32; o <<= 1) { int t = __shfl_up_sync(UG_FULL, incl, o); if (lane >= o) incl += t; }
-    int excl = incl - n, total = __shfl_sync(UG_FULL, incl, 31);
+    for (int o = 1; o < G; o <<= 1) { int t = __shfl_up_sync(gp.mask, incl, o, G); if (l >= o) incl += t; }
+    int excl = incl - n, total = gp.shfl(incl, G - 1);
     if (n > 0) {
       const DevShape& A = M.shapes[sa]; const DevShape& B = M.shapes[sb];
       float mu = fminf(fmaxf(A.mu * B.mu, -UGP_MAX_FRICTION), UGP_MAX_FRICTION);
       float roll = fminf(fmaxf(A.roll * B.mu + B.roll * A.mu, -UGP_MAX_FRICTION), UGP_MAX_FRICTION);
+      const int fa = A.body > 0 ? A.body - 1 : -1, fb = B.body > 0 ? B.body - 1 : -1, ra = A.body == 0 ? A.rbody : -1;
+#pragma unroll 1
       for (int i = 0; i < n; i++) {
         int idx = base + excl + i;
         if (idx < UG_MAXC) {
           Con& c = s.con[idx];
-          c.sa = sa; c.sb = sb; st3(c.posA, pts[i].posA); st3(c.posB, pts[i].posB); st3(c.n, pts[i].n);
+          c.shapes = sa | (sb << 8); c.bodies = (fa + 1) | ((fb + 1) << 8) | ((ra + 1) << 16);
+          st3(c.pa, fa >= 0 ? pts[i].posA - ld3(s.fpos[fa]) : pts[i].posA);
+          st3(c.rb, fb >= 0 ? pts[i].posB - ld3(s.fpos[fb]) : pts[i].posB);
+          st3(c.n, pts[i].n);
           c.dist = pts[i].dist; c.mu = mu; c.rest = A.rest * B.rest; c.roll = i == 0 ? roll : 0.f;
         }
       }
     }
     base = min(base + total, UG_MAXC);
   }
-  if (lane == 0) s.ncon = base;
-  __syncwarp();
+  if (l == 0) s.ncon = base;
+  gp.sync();
 }
 
-// Jacobian contribution of one side of a contact-type row. J is a per-lane register array (static indexing only).
-UG_DEV void add_side(const Smem& s, const DevModel& M, const DevShape& S, f3 P, f3 dir, bool lin, float sgn, float* J) {
-  if (S.body == 0) {
-    uint32_t anc = M.anc[S.rbody];
+// Jacobian of one contact-type row: 12 robot entries plus the linear / angular blocks of the (at most two) free
+// bodies it touches. Register-resident (static indexing only).
+struct CRow {
+  float Jr[UG_NDOF];
+  f3 JlA, JaA, JlB, JaB;
+  int fa, fb;
+};
+
+template <class S>
+UG_DEV void build_crow(const S& s, const DevModel& M, int desc, CRow& r, bool robot_part) {
+  const int k = desc & 255, type = (desc >> 8) & 15, dir = desc >> 12;
+  const Con& c = s.con[k];
+  f3 n = ld3(c.n), t1, t2; plane_space(n, t1, t2);
+  f3 dv = type == RT_NORMAL ? n : (dir == 0 ? t1 : t2);
+  const bool lin = type != RT_ROLL;
+  const int bod = c.bodies;
+  r.fa = (bod & 255) - 1; r.fb = ((bod >> 8) & 255) - 1;
+  const int ra = ((bod >> 16) & 255) - 1;
+  f3 pa = ld3(c.pa), rb = ld3(c.rb);
+  const f3 z = mk3(0, 0, 0);
+  r.JlA = z; r.JaA = z; r.JlB = z; r.JaB = z;
+  if (r.fa >= 0) { r.JlA = lin ? dv : z; r.JaA = lin ? cross(pa, dv) : dv; }
+  if (r.fb >= 0) { r.JlB = lin ? -dv : z; r.JaB = lin ? -cross(rb, dv) : -dv; }
+  if (robot_part) {
+    const uint32_t anc = ra >= 0 ? M.anc[ra] : 0u;
 #pragma unroll
-    for (int d = 0; d < UG_NDOF; d++) if (anc >> d & 1) {
-      f3 a = ld3(s.ax[d]);
-      J[d] += sgn * (lin ? dot(dir, cross(a, P - ld3(s.bp[d]))) : dot(dir, a));
+    for (int d = 0; d < UG_NDOF; d++) {
+      float v = 0.f;
+      if (anc >> d & 1) {
+        f3 a = ld3(s.ax[d]);
+        v = lin ? dot(dv, cross(a, pa - ld3(s.bp[d]))) : dot(dv, a);
+      }
+      r.Jr[d] = v;
     }
-  } else if (S.body > 0) {
-#pragma unroll
-    for (int k = 0; k < UG_MAXFREE; k++) if (S.body - 1 == k) {
-      f3 jl = lin ? dir * sgn : mk3(0, 0, 0);
-      f3 ja = lin ? cross(P - ld3(s.fpos[k]), dir) * sgn : dir * sgn;
-      J[12 + 6 * k] += jl.x; J[13 + 6 * k] += jl.y; J[14 + 6 * k] += jl.z; J[15 + 6 * k] += ja.x; J[16 + 6 * k] += ja.y; J[17 + 6 * k] += ja.z;
-    }
   }
 }
 
-// B = (M^-1 J^T) for a dense 30-wide row held in registers.
-UG_DEV void minv_row(const Smem& s, const DevModel& M, const float* J, float* B) {
-#pragma unroll
-  for (int a = 0; a < UG_NDOF; a++) {
-    float v = 0.f;
-#pragma unroll
-    for (int b = 0; b < UG_NDOF; b++) v += s.M[a][b] * J[b];
-    B[a] = v;
-  }
-#pragma unroll
-  for (int k = 0; k < UG_MAXFREE; k++) {
-    float im = k < M.nfree && (s.flags & (FL_BODY0 << k)) ? 1.0f / M.fmass[k] : 0.f;
-    B[12 + 6 * k] = J[12 + 6 * k] * im; B[13 + 6 * k] = J[13 + 6 * k] * im; B[14 + 6 * k] = J[14 + 6 * k] * im;
-    f3 ba = symv(s.fIinv[k], mk3(J[15 + 6 * k], J[16 + 6 * k], J[17 + 6 * k]));
-    B[15 + 6 * k] = ba.x; B[16 + 6 * k] = ba.y; B[17 + 6 * k] = ba.z;
-  }
-}
-
-struct RowRegs { float rhs, lo, hi, den, mu; int nidx; };
-
-// Builds row `row` (descriptor in s.desc): writes J to shared memory and returns the scalar parameters.
-__device__ __noinline__ void build_row(Smem& s, const DevModel& M, int row, int n_nc, RowRegs& rr) {
-  float J[30];
-#pragma unroll
-  for (int t = 0; t < 30; t++) J[t] = 0.f;
-  int desc = s.desc[row], type = desc & 15, idx = (desc >> 4) & 255, dir = desc >> 12;
-  f3 dirv = mk3(0, 0, 0);
-  if (type == RT_LIM_LO || type == RT_LIM_HI || type == RT_MOTOR) {
-#pragma unroll
-    for (int d = 0; d < UG_NDOF; d++) if (d == idx) J[d] = type == RT_LIM_HI ? -1.0f : 1.0f;
-  } else if (type == RT_GEAR) {
-    int gd = c_gear_dof[idx]; float gr = c_gear_ratio[idx];
-    J[6] = 1.0f;
-#pragma unroll
-    for (int d = 7; d < UG_NDOF; d++) if (d == gd) J[d] = gr;
-  } else if (type != RT_PAD) {
-    const Con& c = s.con[idx];
-    f3 n = ld3(c.n), t1, t2; plane_space(n, t1, t2);
-    dirv = type == RT_NORMAL ? n : (dir == 0 ? t1 : t2);
-    bool lin = type != RT_ROLL;
-    add_side(s, M, M.shapes[c.sa], ld3(c.posA), dirv, lin, 1.0f, J);
-    add_side(s, M, M.shapes[c.sb], ld3(c.posB), dirv, lin, -1.0f, J);
-  }
-  float B[30]; minv_row(s, M, J, B);
-  float den = 0.f, rel = 0.f;
-#pragma unroll
-  for (int t = 0; t < 30; t++) { den += J[t] * B[t]; rel += J[t] * s.vstar[t]; }
-#pragma unroll
-  for (int t = 0; t < 30; t++) s.J[row][t] = J[t];
-  s.J[row][30] = 0.f; s.J[row][31] = 0.f;
-  rr.den = den; rr.mu = 0.f; rr.nidx = 0; rr.lo = 0.f; rr.hi = 0.f; rr.rhs = 0.f;
-  float inv = type == RT_PAD ? 0.f : 1.0f / den;
-  if (type == RT_PAD) rr.den = 1.0f;
-  if (type == RT_LIM_LO || type == RT_LIM_HI) {
-    float pen = type == RT_LIM_LO ? s.q[idx] - M.lower[idx] : M.upper[idx] - s.q[idx];
-    rr.rhs = (-pen * UGP_ERP * UGP_INV_DT - rel) * inv; rr.lo = 0.f; rr.hi = UGP_LIMIT_MAX_IMPULSE;
-  } else if (type == RT_MOTOR) {
-    float want = UGP_MOTOR_KP * (s.tgt[idx] - s.q[idx]) * UGP_INV_DT + (1.0f - UGP_MOTOR_KD) * s.vstar[idx];
-    want = fminf(fmaxf(want, -M.velocity[idx]), M.velocity[idx]);
-    rr.rhs = (want - s.vstar[idx]) * inv; rr.lo = -M.effort[idx] * UGP_DT; rr.hi = M.effort[idx] * UGP_DT;
-  } else if (type == RT_GEAR) {
-    float pe = UGP_GEAR_ERP * (s.q[6] + c_gear_ratio[idx] * s.q[c_gear_dof[idx]]);
-    rr.rhs = (-pe * UGP_ERP * UGP_INV_DT - rel) * inv; rr.lo = -UGP_GEAR_MAX_FORCE * UGP_DT; rr.hi = UGP_GEAR_MAX_FORCE * UGP_DT;
-  } else if (type == RT_NORMAL) {
-    const Con& c = s.con[idx];
-    float pen = c.dist + UGP_LINEAR_SLOP, rest = 0.f;
-    if (fabsf(rel) >= UGP_RESTITUTION_VEL_THRESHOLD) rest = fmaxf(c.rest * -rel, 0.f);
-    float pos_e = 0.f, vel_e = rest - rel;
-    if (pen > 0.f) vel_e -= pen * UGP_INV_DT; else pos_e = -pen * UGP_ERP2 * UGP_INV_DT;
-    rr.rhs = (pos_e + vel_e) * inv; rr.lo = 0.f; rr.hi = 1e10f;
-  } else if (type == RT_ROLL || type == RT_FRIC) {
-    const Con& c = s.con[idx];
-    rr.rhs = -rel * inv; rr.mu = type == RT_ROLL ? c.roll : c.mu; rr.nidx = n_nc + idx;
-  }
-}
+UG_DEV f3 pick3(const f3* a, int b) { return b == 0 ? a[0] : (b == 1 ? a[1] : a[2]); }
 
 // Returns dt * sum |qd| over the 12 joints after the tick (the quantity wait_until_stable thresholds).
-__device__ __noinline__ float solve_and_integrate(Smem& s, const DevModel& M, int lane, int* iters_out) {
-  // ---- row table
-  int n_nc, NC = s.ncon, NT, fr0, R;
+// The sweep loops are kept rolled and small on purpose: one Gauss-Seidel sweep has to stay resident in the ~6 KB L0
+// instruction cache, because it runs 50 times per tick and is ~80 % of the kernel's time (profiles/).
+template <int G, int RC, class S>
+__device__ __noinline__ float solve_and_integrate(S& s, const DevModel& M, const Gp<G> gp, int* iters_out) {
+  constexpr int NSJ = (UG_JMAX + G - 1) / G, NSC = (RC + G - 1) / G, NS = NSJ + NSC;
+  const int l = gp.l;
+  const int NC = s.ncon;
+  UG_T0();
+  // ---- row tables
+  int n_nc, NT, fr0, Rc;
   {
-    bool lim = false;
-    if (lane < 24) { int d = lane >> 1; float pen = (lane & 1) ? M.upper[d] - s.q[d] : s.q[d] - M.lower[d]; lim = !(pen > 0.f); }
-    unsigned lm = __ballot_sync(UG_FULL, lim);
+    int lim = 0;
+    if (l < UG_NDOF) {
+      if (!(s.q[l] - M.lower[l] > 0.f)) lim = 1;
+      else if (!(M.upper[l] - s.q[l] > 0.f)) lim = 2;
+    }
+    unsigned lm = gp.ballot(lim != 0);
     int nl = __popc(lm);
-    if (lim) s.desc[__popc(lm & ((1u << lane) - 1))] = ((lane & 1) ? RT_LIM_HI : RT_LIM_LO) | ((lane >> 1) << 4);
+    if (lim) { const int p_ = __popc(lm & ((1u << l) - 1u)); s.jdesc[p_] = l | ((lim == 1 ? RT_LIM_LO : RT_LIM_HI) << 8) | (l << 12); s.jci4[p_ + 1] = 4 * l; }
     int nm = 0;
-    bool arm = s.flags & FL_ARM, grip = s.flags & FL_GRIP;
-    if (arm) { if (lane < 6) s.desc[nl + lane] = RT_MOTOR | (lane << 4); nm = 6; }
-    if (grip) { if (lane == 0) s.desc[nl + nm] = RT_MOTOR | (6 << 4); nm++; }
-    if (lane < 5) s.desc[nl + nm + lane] = RT_GEAR | (lane << 4);
+    const int fl = s.flags;
+    if (fl & FL_ARM) { if (l < 6) { s.jdesc[nl + l] = l | (RT_MOTOR << 8) | (l << 12); s.jci4[nl + l + 1] = 4 * l; } nm = 6; }
+    if (fl & FL_GRIP) { if (l == 0) { s.jdesc[nl + nm] = 6 | (RT_MOTOR << 8) | (6 << 12); s.jci4[nl + nm + 1] = 4 * 6; } nm++; }
+    if (l < 5) { s.jdesc[nl + nm + l] = (12 + l) | (RT_GEAR << 8) | (l << 12); s.jci4[nl + nm + l + 1] = 4 * (12 + l); }
     n_nc = nl + nm + 5;
-    if (lane < NC) s.desc[n_nc + lane] = RT_NORMAL | (lane << 4);
-    bool rl = lane < NC && s.con[lane].roll > 0.f;
-    unsigned rm = __ballot_sync(UG_FULL, rl);
+    if (l == 0) { s.jci4[0] = 0; s.jci4[n_nc + 1] = 0; }  // slack entries: the sweeps prefetch one row ahead
+    if (l < NC) s.cdesc[l] = l | (RT_NORMAL << 8);
+    bool rl = l < NC && s.con[l].roll > 0.f;
+    unsigned rm = gp.ballot(rl);
     NT = 2 * __popc(rm);
-    if (rl) { int r = __popc(rm & ((1u << lane) - 1)); s.desc[n_nc + NC + 2 * r] = RT_ROLL | (lane << 4); s.desc[n_nc + NC + 2 * r + 1] = RT_ROLL | (lane << 4) | (1 << 12); }
-    fr0 = n_nc + NC + NT;
-    if (fr0 & 1) { if (lane == 0) s.desc[fr0] = RT_PAD; fr0++; }
-    if (lane < NC) { s.desc[fr0 + 2 * lane] = RT_FRIC | (lane << 4); s.desc[fr0 + 2 * lane + 1] = RT_FRIC | (lane << 4) | (1 << 12); }
-    R = fr0 + 2 * NC;
+    if (rl) { int r = __popc(rm & ((1u << l) - 1u)); s.cdesc[NC + 2 * r] = l | (RT_ROLL << 8); s.cdesc[NC + 2 * r + 1] = l | (RT_ROLL << 8) | (1 << 12); }
+    fr0 = NC + NT;
+    if (fr0 & 1) { if (l == 0) s.cdesc[fr0] = RT_PAD << 8; fr0++; }
+    if (l < NC) { s.cdesc[fr0 + 2 * l] = l | (RT_FRIC << 8); s.cdesc[fr0 + 2 * l + 1] = l | (RT_FRIC << 8) | (1 << 12); }
+    Rc = NC > 0 ? fr0 + 2 * NC : 0;
+    if (Rc > RC) Rc = RC;  // cannot happen for the five envs (RC covers 16 contacts + their rolling rows)
   }
-  __syncwarp();
-  // ---- build rows (three slots per lane)
-  RowRegs rr[3];
+  gp.sync();
+  // ---- per-lane row registers: slots [0, NSJ) joint rows, [NSJ, NS) contact rows
+  float w[NS], lam[NS], lamp[NS], rhs[NS], invd[NS], den[NS], lo[NS], hi[NS];
+  int colown[NSJ], nidx[NSC];
 #pragma unroll
-  for (int k = 0; k < 3; k++) {
-    int row = lane + 32 * k;
-    rr[k].rhs = 0.f; rr[k].lo = 0.f; rr[k].hi = 0.f; rr[k].den = 1.0f; rr[k].mu = 0.f; rr[k].nidx = 0;
-    if (row < R) build_row(s, M, row, n_nc, rr[k]);
+  for (int k = 0; k < NS; k++) { w[k] = 0.f; lam[k] = 0.f; lamp[k] = 0.f; rhs[k] = 0.f; invd[k] = 0.f; den[k] = 0.f; lo[k] = 0.f; hi[k] = 0.f; }
+  // joint rows (signed form: a hi-limit row is the unit row with bounds [-max, 0])
+#pragma unroll
+  for (int sj = 0; sj < NSJ; sj++) {
+    const int j = l + G * sj;
+    colown[sj] = 0;
+    if (j < n_nc) {
+      const int dsc = s.jdesc[j], col = dsc & 255, type = (dsc >> 8) & 15, idx = dsc >> 12;
+      colown[sj] = col;
+      const float dn = s.E[col * UG_NCOL + col], inv = 1.0f / dn;
+      den[sj] = dn; invd[sj] = inv;
+      const float vs = s.vstar[type == RT_GEAR ? 6 : idx], qi = s.q[type == RT_GEAR ? 6 : idx];
+      if (type == RT_LIM_LO) {
+        rhs[sj] = (-(qi - M.lower[idx]) * UGP_ERP * UGP_INV_DT - vs) * inv; lo[sj] = 0.f; hi[sj] = UGP_LIMIT_MAX_IMPULSE;
+      } else if (type == RT_LIM_HI) {
+        rhs[sj] = ((M.upper[idx] - qi) * UGP_ERP * UGP_INV_DT - vs) * inv; lo[sj] = -UGP_LIMIT_MAX_IMPULSE; hi[sj] = 0.f;
+      } else if (type == RT_MOTOR) {
+        float want = UGP_MOTOR_KP * (s.tgt[idx] - qi) * UGP_INV_DT + (1.0f - UGP_MOTOR_KD) * vs;
+        want = fminf(fmaxf(want, -M.velocity[idx]), M.velocity[idx]);
+        rhs[sj] = (want - vs) * inv; lo[sj] = -M.effort[idx] * UGP_DT; hi[sj] = M.effort[idx] * UGP_DT;
+      } else {
+        const int gd = c_gear_dof[idx]; const float gr = c_gear_ratio[idx];
+        float rel = vs + gr * s.vstar[gd];
+        float pe = UGP_GEAR_ERP * (qi + gr * s.q[gd]);
+        rhs[sj] = (-pe * UGP_ERP * UGP_INV_DT - rel) * inv; lo[sj] = -UGP_GEAR_MAX_FORCE * UGP_DT; hi[sj] = UGP_GEAR_MAX_FORCE * UGP_DT;
+      }
+    }
   }
-  __syncwarp();
-  // ---- Delassus matrix A = J M^-1 J^T, column(s) of this lane's rows
+  // contact rows, pass 1 (one code copy, slot loop rolled): Jacobian, robot response (-> E), diagonal, right-hand
+  // side. Row parameters go through a scratch area behind the M^-1 copy (dead dynamics temporaries).
+  float* const prm = &s.u.d.cm[0][0];
 #pragma unroll 1
-  for (int k = 0; k < 3; k++) {
-    int row = lane + 32 * k;
-    if (row < R) {
-      float J[30], B[30];
+  for (int so = 0; so * G < Rc; so++) {
+    const int c = l + G * so;
+    if (c < Rc) {
+      const int dsc = s.cdesc[c];
+      const int type = (dsc >> 8) & 15, k = dsc & 255;
+      float4 p0 = make_float4(0.f, 0.f, 0.f, 0.f), p1 = make_float4(0.f, 0.f, 0.f, 0.f);
+      float* Er = s.E + (UG_NCOL + c) * UG_NCOL;
+      if (type != RT_PAD) {
+        CRow r; build_crow(s, M, dsc, r, true);
+        float Br[UG_NDOF];
 #pragma unroll
-      for (int t = 0; t < 30; t++) J[t] = s.J[row][t];
-      minv_row(s, M, J, B);
-      for (int i = 0; i < R; i++) {
-        const float4* Ji = reinterpret_cast<const float4*>(s.J[i]);
-        float v = 0.f;
-#pragma unroll
-        for (int t4 = 0; t4 < 7; t4++) { float4 j4 = Ji[t4]; v += j4.x * B[4 * t4] + j4.y * B[4 * t4 + 1] + j4.z * B[4 * t4 + 2] + j4.w * B[4 * t4 + 3]; }
-        { float4 j4 = Ji[7]; v += j4.x * B[28] + j4.y * B[29]; }
-        s.A[i][row] = v;
-      }
-    }
-  }
-  if (lane == 0) s.nrows = R;
-  for (int r = lane; r < UG_RMAX; r += 32) s.lam[r] = 0.f;
-  __syncwarp();
-  // ---- projected Gauss-Seidel in contact space. Lane owns rows lane, lane+32, lane+64: applied impulse lam[k] and
-  //      w[k] = J_row . (accumulated delta velocity). Sweep order as Bullet's multibody solver (row P6).
-  float lam[3] = {0.f, 0.f, 0.f}, w[3] = {0.f, 0.f, 0.f}, invd[3];
-#pragma unroll
-  for (int k = 0; k < 3; k++) invd[k] = 1.0f / rr[k].den;
-  int it = 0;
-  const int nrm1 = n_nc + NC, tr1 = n_nc + NC + NT;
-#define UG_ROW_STEP(ROW, K, COND_EXTRA)                                                          \
-  {                                                                                              \
-    const int l_ = (ROW) & 31;                                                                   \
-    float d_ = rr[K].rhs - w[K] * invd[K];                                                       \
-    float s_ = fminf(fmaxf(lam[K] + d_, lo_), hi_);                                              \
-    d_ = s_ - lam[K];                                                                            \
-    if (!(COND_EXTRA)) d_ = 0.f;                                                                 \
-    if (lane == l_) { lam[K] += d_; float r_ = d_ * rr[K].den; res = fmaxf(res, r_ * r_); }      \
-    float delta = __shfl_sync(UG_FULL, d_, l_);                                                  \
-    const float* Ar = s.A[ROW];                                                                  \
-    w[0] += Ar[lane] * delta;                                                                    \
-    if (R > 32) w[1] += Ar[lane + 32] * delta;                                                   \
-    if (R > 64 && lane < UG_RMAX - 64) w[2] += Ar[lane + 64] * delta;                            \
-  }
-  for (; it < UGP_SOLVER_ITERS;) {
-    float res = 0.f;
-    // joint rows (all live in slot 0), order alternates with the iteration parity
-    for (int j = 0; j < n_nc; j++) {
-      int row = (it & 1) ? j : n_nc - 1 - j;
-      float lo_ = rr[0].lo, hi_ = rr[0].hi;
-      UG_ROW_STEP(row, 0, true)
-    }
-    // normal rows
-#pragma unroll
-    for (int k = 0; k < 3; k++) {
-      int a = max(n_nc, 32 * k), b = min(nrm1, 32 * k + 32);
-      for (int row = a; row < b; row++) {
-        float lo_ = 0.f, hi_ = 1e10f;
-        UG_ROW_STEP(row, k, true)
-        if (lane == (row & 31)) s.lam[row] = lam[k];
-      }
-    }
-    __syncwarp();
-    // rolling-friction rows: limits follow the normal impulse; skipped while it is zero
-#pragma unroll
-    for (int k = 0; k < 3; k++) {
-      int a = max(nrm1, 32 * k), b = min(tr1, 32 * k + 32);
-      for (int row = a; row < b; row++) {
-        float tot = s.lam[rr[k].nidx];
-        float hi_ = rr[k].mu * tot, lo_ = -hi_;
-        bool on = __shfl_sync(UG_FULL, tot, row & 31) > 0.f;
-        UG_ROW_STEP(row, k, on)
-      }
-    }
-    // friction pairs with the implicit cone
-#pragma unroll
-    for (int k = 0; k < 3; k++) {
-      int a = max(fr0, 32 * k), b = min(R, 32 * k + 32);
-      for (int row = a; row < b; row += 2) {
-        const int l_ = row & 31;
-        float lim = rr[k].mu * s.lam[rr[k].nidx];
-        float d_ = rr[k].rhs - w[k] * invd[k];
-        float sm = lam[k] + d_;
-        float sa = __shfl_sync(UG_FULL, sm, l_), sb = __shfl_sync(UG_FULL, sm, l_ + 1);
-        float lm = __shfl_sync(UG_FULL, lim, l_);
-        float ca = lm, cb = lm;
-        if (sa < -lm || sa > lm || sb < -lm || sb > lm) {
-          float ih = rsqrtf(fmaxf(sa * sa + sb * sb, 1e-30f));
-          ca = fabsf(lm * sa * ih); cb = fabsf(lm * sb * ih);
+        for (int a = 0; a < UG_NDOF; a++) {
+          const float4* Mr = reinterpret_cast<const float4*>(s.u.d.M[a]);
+          float4 m0 = Mr[0], m1 = Mr[1], m2 = Mr[2];
+          Br[a] = m0.x * r.Jr[0] + m0.y * r.Jr[1] + m0.z * r.Jr[2] + m0.w * r.Jr[3] + m1.x * r.Jr[4] + m1.y * r.Jr[5] + m1.z * r.Jr[6] + m1.w * r.Jr[7] +
+                  m2.x * r.Jr[8] + m2.y * r.Jr[9] + m2.z * r.Jr[10] + m2.w * r.Jr[11];
         }
-        float mine = lane == l_ ? ca : cb;
-        float sn = fminf(fmaxf(sm, -mine), mine);
-        d_ = sn - lam[k];
-        if (lane == l_ || lane == l_ + 1) { lam[k] = sn; float r_ = d_ * rr[k].den; res = fmaxf(res, r_ * r_); }
-        float da = __shfl_sync(UG_FULL, d_, l_), db = __shfl_sync(UG_FULL, d_, l_ + 1);
-        const float* Aa = s.A[row]; const float* Ab = s.A[row + 1];
-        w[0] += Aa[lane] * da + Ab[lane] * db;
-        if (R > 32) w[1] += Aa[lane + 32] * da + Ab[lane + 32] * db;
-        if (R > 64 && lane < UG_RMAX - 64) w[2] += Aa[lane + 64] * da + Ab[lane + 64] * db;
+        float dn = 0.f, rel = 0.f;
+#pragma unroll
+        for (int a = 0; a < UG_NDOF; a++) { Er[a] = Br[a]; dn += r.Jr[a] * Br[a]; rel += r.Jr[a] * s.vstar[a]; }
+#pragma unroll
+        for (int gi = 0; gi < 5; gi++) Er[12 + gi] = Br[6] + c_gear_ratio[gi] * Br[7 + gi];
+        if (r.fa >= 0) {
+          const float* v = s.vstar + UG_NDOF + 6 * r.fa;
+          dn += dot(r.JlA, r.JlA) * (1.0f / M.fmass[r.fa]) + dot(r.JaA, symv(s.fIinv[r.fa], r.JaA));
+          rel += dot(r.JlA, ld3(v)) + dot(r.JaA, ld3(v + 3));
+        }
+        if (r.fb >= 0) {
+          const float* v = s.vstar + UG_NDOF + 6 * r.fb;
+          dn += dot(r.JlB, r.JlB) * (1.0f / M.fmass[r.fb]) + dot(r.JaB, symv(s.fIinv[r.fb], r.JaB));
+          rel += dot(r.JlB, ld3(v)) + dot(r.JaB, ld3(v + 3));
+        }
+        const float inv = 1.0f / dn;
+        p0.y = inv; p0.z = dn;
+        const Con& cn = s.con[k];
+        if (type == RT_NORMAL) {
+          float pen = cn.dist + UGP_LINEAR_SLOP, rest = 0.f;
+          if (fabsf(rel) >= UGP_RESTITUTION_VEL_THRESHOLD) rest = fmaxf(cn.rest * -rel, 0.f);
+          float pos_e = 0.f, vel_e = rest - rel;
+          if (pen > 0.f) vel_e -= pen * UGP_INV_DT; else pos_e = -pen * UGP_ERP2 * UGP_INV_DT;
+          p0.x = (pos_e + vel_e) * inv; p0.w = 0.f; p1.x = 1e10f;
+        } else {
+          p0.x = -rel * inv; p1.x = type == RT_ROLL ? cn.roll : cn.mu; p1.y = __int_as_float(k);
+        }
+      } else {
+#pragma unroll
+        for (int a = 0; a < UG_NCOL; a++) Er[a] = 0.f;
+      }
+      reinterpret_cast<float4*>(prm)[2 * c] = p0; reinterpret_cast<float4*>(prm)[2 * c + 1] = p1;
+    }
+  }
+#pragma unroll
+  for (int so = 0; so < NSC; so++) {
+    const int c = l + G * so;
+    nidx[so] = 0;
+    if (c < Rc) {
+      float4 p0 = reinterpret_cast<const float4*>(prm)[2 * c], p1 = reinterpret_cast<const float4*>(prm)[2 * c + 1];
+      rhs[NSJ + so] = p0.x; invd[NSJ + so] = p0.y; den[NSJ + so] = p0.z; lo[NSJ + so] = p0.w; hi[NSJ + so] = p1.x; nidx[so] = __float_as_int(p1.y);
+    }
+  }
+  gp.sync();
+  UG_TP(3)
+  // contact rows, pass 2: T(c, c') = J_c' . (M^-1 J_c^T) for c' <= c. The owner of row c keeps its Jacobian and its
+  // free-body responses in registers; the loop over c' is group-uniform.
+#pragma unroll 1
+  for (int so = 0; so * G < Rc; so++) {
+    const int c = l + G * so;
+    const bool has = c < Rc;
+    const int dsc = has ? s.cdesc[c] : (RT_PAD << 8);
+    CRow r;
+    f3 dl[UG_MAXFREE], da[UG_MAXFREE];
+#pragma unroll
+    for (int b = 0; b < UG_MAXFREE; b++) { dl[b] = mk3(0, 0, 0); da[b] = mk3(0, 0, 0); }
+#pragma unroll
+    for (int d = 0; d < UG_NDOF; d++) r.Jr[d] = 0.f;
+    if (((dsc >> 8) & 15) != RT_PAD) {
+      build_crow(s, M, dsc, r, true);
+#pragma unroll
+      for (int b = 0; b < UG_MAXFREE; b++) {
+        if (r.fa == b) { dl[b] = r.JlA * (1.0f / M.fmass[b]); da[b] = symv(s.fIinv[b], r.JaA); }
+        if (r.fb == b) { dl[b] = r.JlB * (1.0f / M.fmass[b]); da[b] = symv(s.fIinv[b], r.JaB); }
       }
     }
+    const int cmax = min(Rc, so * G + G);
+    float* Trow = s.u.T + c * RC;
+#pragma unroll 1
+    for (int cp = 0; cp < cmax; cp++) {
+      const int dp = s.cdesc[cp], tp = (dp >> 8) & 15;
+      float acc = 0.f;
+      if (tp != RT_PAD) {
+        const Con& cn = s.con[dp & 255];
+        f3 n = ld3(cn.n), t1, t2; plane_space(n, t1, t2);
+        f3 dv = tp == RT_NORMAL ? n : ((dp >> 12) == 0 ? t1 : t2);
+        const float* Ep = s.E + (UG_NCOL + cp) * UG_NCOL;
+#pragma unroll
+        for (int d = 0; d < UG_NDOF; d++) acc += r.Jr[d] * Ep[d];
+        const int bod = cn.bodies, fa = (bod & 255) - 1, fb = ((bod >> 8) & 255) - 1;
+        if (fa >= 0) {
+          f3 a = pick3(da, fa);
+          f3 vel = tp == RT_ROLL ? a : pick3(dl, fa) + cross(a, ld3(cn.pa));
+          acc += dot(dv, vel);
+        }
+        if (fb >= 0) {
+          f3 a = pick3(da, fb);
+          f3 vel = tp == RT_ROLL ? a : pick3(dl, fb) + cross(a, ld3(cn.rb));
+          acc -= dot(dv, vel);
+        }
+      }
+      if (has) { Trow[cp] = acc; if (cp < so * G) s.u.T[cp * RC + c] = acc; }  // rows of earlier slots get their upper part here
+    }
+  }
+  gp.sync();
+  UG_TP(4)
+  // ---- projected Gauss-Seidel, Bullet's sweep order (row P6). Operands are addressed with 32-bit shared addresses:
+  //      a step of row r reads E / T at (uniform row offset) + (per-lane constant) + (per-slot immediate).
+  const unsigned aE = smem_u32(s.E), aT = smem_u32(s.u.T);
+  unsigned aEj[NSJ], aEq[NSJ];
+#pragma unroll
+  for (int k = 0; k < NSJ; k++) { aEj[k] = aE + 4u * (unsigned)(colown[k] * UG_NCOL); aEq[k] = aE + 4u * (unsigned)(UG_NCOL * UG_NCOL + colown[k]); }
+  const unsigned aEc = aE + 4u * (unsigned)((UG_NCOL + l) * UG_NCOL);  // contact slot o: + o * G * UG_NCOL * 4
+  const unsigned aTl = aT + 4u * (unsigned)l;                           // row r: + r * RC * 4; contact slot o: + o * G * 4
+  float limv[NSC];
+#pragma unroll
+  for (int so = 0; so < NSC; so++) limv[so] = 0.f;
+  // Operand loads are written BEFORE the clamp / shuffle chain of each step on purpose: every shuffle ends a basic
+  // block (convergence check), ptxas does not move loads across it, and a load issued after the shuffle would put
+  // its ~29-cycle latency on the step's critical path. Issued first, it overlaps the chain (profiles/ r01d -> r01e).
+  //
+  // One Gauss-Seidel step of a joint row: ROW is group-uniform, SJ its (unrolled) slot, NACT the number of contact
+  // slots in use this tick (sweeps are instantiated per NACT so that the loop bodies carry no dead predicates).
+  // CI is the row's column byte offset, loaded one iteration ahead; NEXT is the following row of the sweep.
+#define UG_JOINT_STEP(ROW, NEXT, SJ, NACT)                                                               \
+  {                                                                                                      \
+    const unsigned ci_ = ci_cur;                                                                         \
+    float ej_[NSJ], ec_[NACT > 0 ? NACT : 1];                                                            \
+    _Pragma("unroll") for (int k_ = 0; k_ < NSJ; k_++) ej_[k_] = lds(aEj[k_] + ci_);                     \
+    _Pragma("unroll") for (int o_ = 0; o_ < (NACT); o_++) ec_[o_] = lds(aEc + ci_ + 4u * (unsigned)(o_ * G * UG_NCOL)); \
+    ci_cur = (unsigned)s.jci4[(NEXT) + 1];                                                               \
+    const int li_ = (ROW) - (SJ) * G;                                                                    \
+    float d_ = fmaf(-w[SJ], invd[SJ], rhs[SJ]);                                                          \
+    d_ = fminf(fmaxf(d_, lo[SJ] - lam[SJ]), hi[SJ] - lam[SJ]);                                           \
+    const float delta = gp.shfl(d_, li_);                                                                \
+    if (l == li_) lam[SJ] += delta;                                                                      \
+    _Pragma("unroll") for (int k_ = 0; k_ < NSJ; k_++) w[k_] = fmaf(ej_[k_], delta, w[k_]);              \
+    _Pragma("unroll") for (int o_ = 0; o_ < (NACT); o_++) w[NSJ + o_] = fmaf(ec_[o_], delta, w[NSJ + o_]); \
+  }
+  // operands of a contact-row step (rows ROW and, when PAIR, ROW + 1): E entries for the joint slots, T entries for
+  // the contact slots
+#define UG_CONTACT_LOAD(ROW, PAIR, NACT)                                                                 \
+    const unsigned er_ = 4u * (unsigned)((ROW) * UG_NCOL), tr_ = aTl + 4u * (unsigned)((ROW) * RC);      \
+    float uj_[NSJ], vj_[NSJ], uc_[NACT], vc_[NACT];                                                      \
+    _Pragma("unroll") for (int k_ = 0; k_ < NSJ; k_++) { uj_[k_] = lds(aEq[k_] + er_); vj_[k_] = (PAIR) ? lds(aEq[k_] + er_ + 4u * UG_NCOL) : 0.f; } \
+    _Pragma("unroll") for (int o_ = 0; o_ < (NACT); o_++) { uc_[o_] = lds(tr_ + 4u * (unsigned)(o_ * G)); vc_[o_] = (PAIR) ? lds(tr_ + 4u * (unsigned)(RC + o_ * G)) : 0.f; }
+#define UG_CONTACT_APPLY(DA, DB, PAIR, NACT)                                                             \
+    _Pragma("unroll") for (int k_ = 0; k_ < NSJ; k_++) { w[k_] = fmaf(uj_[k_], DA, w[k_]); if (PAIR) w[k_] = fmaf(vj_[k_], DB, w[k_]); } \
+    _Pragma("unroll") for (int o_ = 0; o_ < (NACT); o_++) { w[NSJ + o_] = fmaf(uc_[o_], DA, w[NSJ + o_]); if (PAIR) w[NSJ + o_] = fmaf(vc_[o_], DB, w[NSJ + o_]); }
+  // joint rows, order alternates with the iteration parity (backward on even sweeps)
+#define UG_JOINT_SWEEP(NACT)                                                                             \
+  if (it & 1) {                                                                                          \
+    unsigned ci_cur = (unsigned)s.jci4[1];                                                               \
+    _Pragma("unroll") for (int sj = 0; sj < NSJ; sj++) {                                                 \
+      const int b_ = min(n_nc, sj * G + G);                                                              \
+      _Pragma("unroll 1") for (int row = sj * G; row < b_; row++) UG_JOINT_STEP(row, row + 1, sj, NACT)  \
+    }                                                                                                    \
+  } else {                                                                                               \
+    unsigned ci_cur = (unsigned)s.jci4[n_nc];                                                            \
+    _Pragma("unroll") for (int sj = NSJ - 1; sj >= 0; sj--) {                                            \
+      _Pragma("unroll 1") for (int row = min(n_nc, sj * G + G) - 1; row >= sj * G; row--) UG_JOINT_STEP(row, row - 1, sj, NACT) \
+    }                                                                                                    \
+  }
+  // normals (contacts 0..NC-1 live in contact slot 0: NC <= 16 <= G), friction limits from this sweep's normal
+  // impulses, rolling-friction rows (Golf only; skipped while the normal impulse is zero), friction pairs with the
+  // implicit cone
+#define UG_CONTACT_SWEEP(NACT)                                                                           \
+  {                                                                                                      \
+    _Pragma("unroll 1") for (int row = 0; row < NC; row++) {                                             \
+      UG_CONTACT_LOAD(row, false, NACT)                                                                  \
+      float d_ = fmaf(-w[NSJ], invd[NSJ], rhs[NSJ]);                                                     \
+      d_ = fminf(fmaxf(d_, lo[NSJ] - lam[NSJ]), hi[NSJ] - lam[NSJ]);                                     \
+      const float delta = gp.shfl(d_, row);                                                              \
+      if (l == row) lam[NSJ] += delta;                                                                   \
+      UG_CONTACT_APPLY(delta, 0.f, false, NACT)                                                          \
+    }                                                                                                    \
+    _Pragma("unroll") for (int so = 0; so < (NACT); so++) limv[so] = hi[NSJ + so] * gp.shfl(lam[NSJ], nidx[so]); \
+    if (NT > 0) {                                                                                        \
+      _Pragma("unroll") for (int so = 0; so < (NACT); so++) {                                            \
+        const int a_ = max(NC, so * G), b_ = min(NC + NT, so * G + G);                                   \
+        _Pragma("unroll 1") for (int row = a_; row < b_; row++) {                                        \
+          UG_CONTACT_LOAD(row, false, NACT)                                                              \
+          const float bnd = limv[so];                                                                    \
+          float d_ = fmaf(-w[NSJ + so], invd[NSJ + so], rhs[NSJ + so]);                                  \
+          d_ = fminf(fmaxf(d_, -bnd - lam[NSJ + so]), bnd - lam[NSJ + so]);                              \
+          if (!(bnd > 0.f)) d_ = 0.f;                                                                    \
+          const float delta = gp.shfl(d_, row - so * G);                                                 \
+          if (l == row - so * G) lam[NSJ + so] += delta;                                                 \
+          UG_CONTACT_APPLY(delta, 0.f, false, NACT)                                                      \
+        }                                                                                                \
+      }                                                                                                  \
+    }                                                                                                    \
+    _Pragma("unroll") for (int so = 0; so < (NACT); so++) {                                              \
+      const int a_ = max(fr0, so * G), b_ = min(Rc, so * G + G);                                         \
+      _Pragma("unroll 1") for (int row = a_; row < b_; row += 2) {                                       \
+        UG_CONTACT_LOAD(row, true, NACT)                                                                 \
+        const int li = row - so * G;                                                                     \
+        float d_ = fmaf(-w[NSJ + so], invd[NSJ + so], rhs[NSJ + so]);                                    \
+        const float sm = lam[NSJ + so] + d_;                                                             \
+        const float ot = __shfl_xor_sync(gp.mask, sm, 1, G); /* the pair's other tangent (pairs start on even rows) */ \
+        const float lm = limv[so];                           /* both lanes of a pair carry the same limit */ \
+        float cl = lm;                                                                                   \
+        if (fabsf(sm) > lm || fabsf(ot) > lm) cl = fabsf(lm * sm * rsqrtf(fmaxf(sm * sm + ot * ot, 1e-30f))); \
+        const float sn = fminf(fmaxf(sm, -cl), cl);                                                      \
+        d_ = sn - lam[NSJ + so];                                                                         \
+        if ((l | 1) == (li | 1)) lam[NSJ + so] = sn;                                                     \
+        const float dA = gp.shfl(d_, li), dB = gp.shfl(d_, li + 1);                                      \
+        UG_CONTACT_APPLY(dA, dB, true, NACT)                                                             \
+      }                                                                                                  \
+    }                                                                                                    \
+  }
+  const int nact = (Rc + G - 1) / G;
+  int it = 0;
+#pragma unroll 1
+  for (; it < UGP_SOLVER_ITERS;) {
+    if (nact == 0) { UG_JOINT_SWEEP(0) }
+    else if (nact == 1) { UG_JOINT_SWEEP(1) UG_CONTACT_SWEEP(1) }
+    else if (NSC >= 2 && nact == 2) { UG_JOINT_SWEEP(2) UG_CONTACT_SWEEP(2) }
+    else if (NSC >= 3 && nact == 3) { UG_JOINT_SWEEP(3) UG_CONTACT_SWEEP(3) }
+    else if (NSC >= 4) { UG_JOINT_SWEEP(4) UG_CONTACT_SWEEP(4) }
     it++;
-    res = warp_max(res);
+    // least-squares residual of the sweep: max over rows of the squared velocity change (Bullet's early exit)
+    float res = 0.f;
+#pragma unroll
+    for (int k = 0; k < NS; k++) { float r_ = (lam[k] - lamp[k]) * den[k]; res = fmaxf(res, r_ * r_); lamp[k] = lam[k]; }
+    res = gp.max(res);
     if (res <= UGP_RESIDUAL_THRESHOLD) break;
   }
-#undef UG_ROW_STEP
+#undef UG_JOINT_STEP
+#undef UG_CONTACT_LOAD
+#undef UG_CONTACT_APPLY
+#undef UG_JOINT_SWEEP
+#undef UG_CONTACT_SWEEP
   *iters_out = it;
-  // ---- generalized impulse g = J^T lambda, delta velocity, integration
+  UG_TP(5)
+  // ---- velocity change: robot dv from the stored responses, free bodies from the summed generalized impulse
 #pragma unroll
-  for (int k = 0; k < 3; k++) { int row = lane + 32 * k; if (row < R) s.lam[row] = lam[k]; }
-  __syncwarp();
-  {
-    float gt = 0.f;
-    for (int r = 0; r < R; r++) gt += s.J[r][lane] * s.lam[r];
-    s.g[lane] = gt;
+  for (int sj = 0; sj < NSJ; sj++) { const int j = l + G * sj; if (j < n_nc) s.lam[j] = lam[sj]; }
+#pragma unroll
+  for (int so = 0; so < NSC; so++) { const int c = l + G * so; if (c < Rc) s.lam[UG_JMAX + c] = lam[NSJ + so]; }
+  gp.sync();
+  f3 gl[UG_MAXFREE], ga[UG_MAXFREE];
+#pragma unroll
+  for (int b = 0; b < UG_MAXFREE; b++) { gl[b] = mk3(0, 0, 0); ga[b] = mk3(0, 0, 0); }
+  if (Rc > 0) {
+#pragma unroll 1
+    for (int c = l; c < Rc; c += G) {
+      const int dsc = s.cdesc[c];
+      if (((dsc >> 8) & 15) != RT_PAD) {
+        CRow r; build_crow(s, M, dsc, r, false);
+        const float lm = s.lam[UG_JMAX + c];
+#pragma unroll
+        for (int b = 0; b < UG_MAXFREE; b++) {
+          if (r.fa == b) { gl[b] = gl[b] + r.JlA * lm; ga[b] = ga[b] + r.JaA * lm; }
+          if (r.fb == b) { gl[b] = gl[b] + r.JlB * lm; ga[b] = ga[b] + r.JaB * lm; }
+        }
+      }
+    }
+#pragma unroll
+    for (int b = 0; b < UG_MAXFREE; b++) {
+      gl[b] = mk3(gp.sum(gl[b].x), gp.sum(gl[b].y), gp.sum(gl[b].z));
+      ga[b] = mk3(gp.sum(ga[b].x), gp.sum(ga[b].y), gp.sum(ga[b].z));
+    }
   }
-  __syncwarp();
   float absq = 0.f;
-  if (lane < UG_NDOF) {
+  if (l < UG_NDOF) {
     float dv = 0.f;
-#pragma unroll
-    for (int b = 0; b < UG_NDOF; b++) dv += s.M[lane][b] * s.g[b];
-    float v = fminf(fmaxf(s.vstar[lane] + dv, -UGP_MAX_COORD_VEL), UGP_MAX_COORD_VEL);
-    s.qd[lane] = v; s.q[lane] += UGP_DT * v;
+#pragma unroll 1
+    for (int j = 0; j < n_nc; j++) dv = fmaf(s.lam[j], s.E[(s.jdesc[j] & 255) * UG_NCOL + l], dv);
+#pragma unroll 1
+    for (int c = 0; c < Rc; c++) dv = fmaf(s.lam[UG_JMAX + c], s.E[(UG_NCOL + c) * UG_NCOL + l], dv);
+    float v = fminf(fmaxf(s.vstar[l] + dv, -UGP_MAX_COORD_VEL), UGP_MAX_COORD_VEL);
+    s.qd[l] = v; s.q[l] += UGP_DT * v;
     absq = fabsf(UGP_DT * v);
-  } else if (lane < UG_NDOF + UG_MAXFREE) {
-    int b = lane - UG_NDOF;
+  } else if (l < UG_NDOF + UG_MAXFREE) {
+    int b = l - UG_NDOF;
     if (b < M.nfree && (s.flags & (FL_BODY0 << b))) {
-      const float* gb = s.g + UG_NDOF + 6 * b; const float* vb = s.vstar + UG_NDOF + 6 * b;
+      const float* vb = s.vstar + UG_NDOF + 6 * b;
       float im = 1.0f / M.fmass[b];
-      f3 lin = ld3(vb) + ld3(gb) * im;
-      f3 ang = ld3(vb + 3) + symv(s.fIinv[b], ld3(gb + 3));
+      f3 lin = ld3(vb) + pick3(gl, b) * im;
+      f3 ang = ld3(vb + 3) + symv(s.fIinv[b], pick3(ga, b));
       st3(s.flin[b], lin); st3(s.fang[b], ang);
       st3(s.fpos[b], ld3(s.fpos[b]) + lin * UGP_DT);
       float wn = norm3(ang);
@@ -344,21 +512,21 @@ __device__ __noinline__ float solve_and_integrate(Smem& s, const DevModel& M, in
       s.fquat[b][0] = qn.x; s.fquat[b][1] = qn.y; s.fquat[b][2] = qn.z; s.fquat[b][3] = qn.w;
     }
   }
-  absq = warp_sum(absq);
-  __syncwarp();
+  absq = gp.sum(absq);
+  gp.sync();
+  UG_TP(6)
   return absq;
 }
 
 // One stepSimulation tick. Returns sum over joints of |q(t) - q(t-1)|.
-UG_DEV float tick(Smem& s, const DevModel& M, int lane, int* iters) {
-  UG_TR("tick: fk\n");
-  fk_bodies(s, M, lane);
-  UG_TR("tick: collide\n");
-  collide(s, M, lane);
-  UG_TR("tick: dynamics ncon=%d\n", s.ncon);
-  dynamics(s, M, lane);
-  UG_TR("tick: solve\n");
-  float r = solve_and_integrate(s, M, lane, iters);
-  UG_TR("tick: done moved=%g iters=%d rows=%d\n", r, *iters, s.nrows);
-  return r;
+template <int G, int RC, class S>
+UG_DEV float tick(S& s, const DevModel& M, const Gp<G>& gp, int* iters) {
+  UG_T0();
+  fk_bodies(s, M, gp);
+  UG_TP(0)
+  collide(s, M, gp);
+  UG_TP(1)
+  dynamics(s, M, gp);
+  UG_TP(2)
+  return solve_and_integrate<G, RC>(s, M, gp, iters);
 }

@@ -3,8 +3,8 @@
 #pragma once
 #include "dev_env.cuh"
 
-template <int ENV>
-UG_DEV void observe(Smem& s, const DevModel& M, float* o, int lane) {
+template <int ENV, class S>
+UG_DEV void observe(S& s, const DevModel& M, float* o, int lane) {
   // caller guarantees fresh fk_bodies(); every lane computes, lane 0 writes
   f3 ep; m3 eR; ee_pose(s, M, ep, eR);
   float v[17];
@@ -36,20 +36,28 @@ UG_DEV void observe(Smem& s, const DevModel& M, float* o, int lane) {
   }
 }
 
-template <int ENV>
+// contact-row capacity per env type: 16 manifold points x 3 rows, plus up to 6 rolling-friction rows in Golf
+template <int ENV> struct EnvRC { static constexpr int value = ENV == 4 ? 54 : 48; };
+
+template <int ENV, int G>
 __global__ void __launch_bounds__(32) env_kernel(KParams P) {
+  using S = SmemT<EnvRC<ENV>::value>;
+  constexpr int RC = EnvRC<ENV>::value;
   extern __shared__ __align__(16) unsigned char smraw[];
-  Smem& s = *reinterpret_cast<Smem*>(smraw);
+  const Gp<G> gp = make_gp<G>();
+  S& s = reinterpret_cast<S*>(smraw)[(threadIdx.x & 31) / G];
   const DevModel& M = *P.model;
-  const int env = blockIdx.x, lane = threadIdx.x;
+  const int env = blockIdx.x * (32 / G) + (threadIdx.x & 31) / G, lane = gp.l;
   constexpr int OD = ENV == 0 ? 6 : (ENV == 3 ? 17 : 9);
   constexpr int AD = ENV == 3 ? 9 : 3;
+  if (env >= P.N) return;
   if (P.mode == MODE_RESET && P.mask && !P.mask[env]) return;
   float* rec = P.state + (size_t)env * UG_STATE;
-  load_state(s, rec, lane);
-  int step_count = (int)s.st[32], episode = (int)s.st[33];
-  q4 vert = mkq(s.st[34], s.st[35], s.st[36], s.st[37]);
-  float ep_ret = s.st[77];
+  load_state(s, rec, gp);
+  int step_count = (int)s.u.st[32], episode = (int)s.u.st[33];
+  q4 vert = mkq(s.u.st[34], s.u.st[35], s.u.st[36], s.u.st[37]);
+  float ep_ret = s.u.st[77];
+  gp.sync();
   const unsigned gidx = (unsigned)(P.gidx0 + env);
   const float* dr = P.draws ? P.draws + 4 * env : nullptr;
   int phase, n = 0, limit = UGP_SETTLE_MAX_TICKS, ticks_step = 0, ticks_reset = 0;
@@ -62,14 +70,14 @@ __global__ void __launch_bounds__(32) env_kernel(KParams P) {
   else {
     phase = PH_STEP;
     const float* a = P.action + (size_t)AD * env;
-    fk_bodies(s, M, lane);
+    fk_bodies(s, M, gp);
     f3 ep; m3 eR; ee_pose(s, M, ep, eR);
     if (ENV == 0 || ENV == 1) {          // env_ball_balance_v0.py:112-118
       if (ENV == 1) rew -= fabsf(a[0]) + fabsf(a[1]) + fabsf(a[2]);
       f3 e = euler_from_quat(mat_to_quat(eR));
-      move_ee(s, M, ep, quat_from_euler(e.x + a[0], e.y + a[1], e.z + a[2]), lane);
+      move_ee(s, M, ep, quat_from_euler(e.x + a[0], e.y + a[1], e.z + a[2]), gp);
     } else if (ENV == 2 || ENV == 4) {   // env_cubes_push_v0.py:122-126, env_golf_v0.py:122-126
-      move_ee(s, M, ep + mk3(a[0], a[1], a[2]), vert, lane);
+      move_ee(s, M, ep + mk3(a[0], a[1], a[2]), vert, gp);
     } else {                              // env_cubes_grasp_v0.py:121-144
       float a0 = a[0], a1 = a[1];
       float u = P.u ? P.u[env] : urand(P.seed, gidx, (unsigned)episode, 16u + (unsigned)step_count);
@@ -84,24 +92,24 @@ __global__ void __launch_bounds__(32) env_kernel(KParams P) {
   // robot.py:85-101: arm to rest pose with zero velocity; task objects removed; episode counters restart
   auto begin_reset = [&]() {
     episode++; step_count = 0; ep_ret = 0.f;
-    __syncwarp();
+    gp.sync();
     if (lane == 0) s.flags &= (FL_ARM | FL_GRIP);
     if (lane < 6) { s.q[lane] = c_rest_pose[lane]; s.qd[lane] = 0.f; }
     phase = PH_ARM10; n = 0; limit = UGP_RESET_ARM_TICKS;
-    __syncwarp();
+    gp.sync();
   };
   if (phase == PH_ARM10) begin_reset();
-  __syncwarp();
+  gp.sync();
 
   // ---- the tick loop
   for (;;) {
     int iters;
-    float moved = tick(s, M, lane, &iters);
+    float moved = tick<G, RC>(s, M, gp, &iters);
     n++; tick_total++;
     bool done = phase == PH_ARM10 || phase == PH_RAW ? n >= limit : (moved < UGP_SETTLE_THRESHOLD || n >= limit);
     if (!done) continue;
     if (phase == PH_RAW) break;
-    fk_bodies(s, M, lane);
+    fk_bodies(s, M, gp);
     f3 ep; m3 eR; ee_pose(s, M, ep, eR);
     if (phase == PH_STEP) {
       ticks_step = n;
@@ -132,7 +140,7 @@ __global__ void __launch_bounds__(32) env_kernel(KParams P) {
         float d = norm3(gc - ld3(s.fpos[0]));
         bool grasp_now = touch_robot(s, M, 11, 13, 1, -1) && touch_robot(s, M, 16, 18, 1, -1);
         int fl = s.flags;
-        __syncwarp();
+        gp.sync();
         if (!(fl & FL_APPROACHED)) {
           rew += geometric_distance_reward(d, 0.5f, 2.f) / 4.f;
           if (d < 0.05f && gripper_opening(s, M) > 0.50f) { fl |= FL_APPROACHED; rew += 5.f; }
@@ -155,12 +163,12 @@ __global__ void __launch_bounds__(32) env_kernel(KParams P) {
         }
         rew -= 0.1f;
       }
-      __syncwarp();
+      gp.sync();
       step_count++; ep_ret += rew;
       trunc = step_count >= M.max_steps;
       if (P.contacts) {
         int nc = s.ncon;
-        if (lane < UG_MAXC) { P.contacts[((size_t)env * UG_MAXC + lane) * 2] = lane < nc ? s.con[lane].sa : -1; P.contacts[((size_t)env * UG_MAXC + lane) * 2 + 1] = lane < nc ? s.con[lane].sb : -1; }
+        if (lane < UG_MAXC) { P.contacts[((size_t)env * UG_MAXC + lane) * 2] = lane < nc ? (s.con[lane].shapes & 255) : -1; P.contacts[((size_t)env * UG_MAXC + lane) * 2 + 1] = lane < nc ? (s.con[lane].shapes >> 8) : -1; }
         if (lane == 0) P.ccount[env] = nc;
       }
       observe<ENV>(s, M, P.obs + (size_t)OD * env, lane);
@@ -177,7 +185,7 @@ __global__ void __launch_bounds__(32) env_kernel(KParams P) {
       // ---------------- reset stage 1 (robot.py:100-101 opens the gripper, then the env-specific first move)
       move_gripper(s, 0.085f, lane);
       if (ENV == 0 || ENV == 1) {          // env_ball_balance_v0.py:154-158
-        move_ee(s, M, mk3(0.0f, -0.60f, 0.60f), mkq(0.50f, -0.50f, -0.50f, 0.50f), lane);
+        move_ee(s, M, mk3(0.0f, -0.60f, 0.60f), mkq(0.50f, -0.50f, -0.50f, 0.50f), gp);
         move_gripper(s, 0.085f * 0.2f, lane);
         phase = PH_SETTLE1;
       } else if (ENV == 2) {               // env_cubes_push_v0.py:212-227,238-246
@@ -186,23 +194,23 @@ __global__ void __launch_bounds__(32) env_kernel(KParams P) {
         spawn(s, 0, mk3(0.0f, -0.5f, 0.1f), lane); spawn(s, 1, c1, lane);
         float sh, ch; sincosf(0.25f * UGP_PI, &sh, &ch);
         vert = mkq(0.f, sh, 0.f, ch);
-        move_ee(s, M, c1 + mk3(0.f, 0.f, 0.2f), vert, lane);
+        move_ee(s, M, c1 + mk3(0.f, 0.f, 0.2f), vert, gp);
         move_gripper(s, 0.0f, lane);
         phase = PH_SETTLE2;
       } else if (ENV == 3) {               // env_cubes_grasp_v0.py:276-299,311-327
         float d0 = dr ? dr[0] : urand(P.seed, gidx, (unsigned)episode, 0u), d1 = dr ? dr[1] : urand(P.seed, gidx, (unsigned)episode, 1u);
         float r = 0.5f + 0.3f * d0, th = -UGP_PI + UGP_PI * d1, sn, cs; sincosf(th, &sn, &cs);
         spawn(s, 0, mk3(r * cs, r * sn, 0.1f), lane);
-        move_ee(s, M, ep, link_quat_chain(s.q, M, 7), lane);
+        move_ee(s, M, ep, link_quat_chain(s.q, M, 7), gp);
         phase = PH_SETTLE2;
       } else {                             // env_golf_v0.py:238-256
         vert = mkq(0.0f, 0.0f, -0.70f, 0.70f);
-        move_ee(s, M, mk3(0.0f, -0.60f, 0.40f), vert, lane);
+        move_ee(s, M, mk3(0.0f, -0.60f, 0.40f), vert, gp);
         move_gripper(s, 0.085f * 0.2f, lane);
         phase = PH_SETTLE1;
       }
       n = 0; limit = UGP_SETTLE_MAX_TICKS;
-      __syncwarp();
+      gp.sync();
       continue;
     }
     if (phase == PH_SETTLE1) {
@@ -225,7 +233,7 @@ __global__ void __launch_bounds__(32) env_kernel(KParams P) {
       }
       move_gripper(s, 0.0f, lane);
       phase = PH_SETTLE2; n = 0; limit = UGP_SETTLE_MAX_TICKS;
-      __syncwarp();
+      gp.sync();
       continue;
     }
     // PH_SETTLE2: reset finished -> first observation of the new episode
@@ -237,7 +245,7 @@ __global__ void __launch_bounds__(32) env_kernel(KParams P) {
     else if (lane == 0) P.nticks[env] = P.mode == MODE_RESET ? ticks_reset : n;
   }
   if (lane == 0 && P.stats) { if (P.mode == MODE_STEP) atomicAdd(&P.stats[4], 1.0); atomicAdd(&P.stats[5], (double)tick_total); }
-  store_state(s, rec, lane, step_count, episode, vert, ep_ret);
+  store_state(s, rec, gp, step_count, episode, vert, ep_ret);
 }
 
 // ---- stand-alone kinematics kernels (one thread per query)
@@ -267,14 +275,16 @@ __global__ void ik_kernel(const DevModel* Mp, int n, const float* q, const float
   for (int k = 0; k < 6; k++) out[6 * (size_t)i + k] = o[k];
 }
 // one warp per query (reuses the warp-level FK)
+typedef SmemT<48> SmemKin;
 __global__ void __launch_bounds__(32) gripper_center_kernel(const DevModel* Mp, int n, const float* q, float* out) {
   extern __shared__ __align__(16) unsigned char smraw[];
-  Smem& s = *reinterpret_cast<Smem*>(smraw);
+  SmemKin& s = *reinterpret_cast<SmemKin*>(smraw);
+  const Gp<32> gp = make_gp<32>();
   int i = blockIdx.x, lane = threadIdx.x;
   if (lane < UG_NDOF) s.q[lane] = q[(size_t)UG_NDOF * i + lane];
   if (lane < UG_MAXFREE) { s.fquat[lane][0] = 0; s.fquat[lane][1] = 0; s.fquat[lane][2] = 0; s.fquat[lane][3] = 1; }
-  __syncwarp();
-  fk_bodies(s, *Mp, lane);
+  gp.sync();
+  fk_bodies(s, *Mp, gp);
   f3 c = gripper_center(s, *Mp);
   if (lane == 0) { out[3 * (size_t)i] = c.x; out[3 * (size_t)i + 1] = c.y; out[3 * (size_t)i + 2] = c.z; }
 }
