@@ -11,6 +11,7 @@
 //
 // Only tests/, __graft_entry__.smoke() and bench.py's cpu_baseline / --impl reference legs may load this library.
 #include <cstdio>
+#include <initializer_list>
 
 #include "urgo_engine.h"
 
@@ -46,25 +47,48 @@ struct Env {
   bool sparse = false;
   int last_contacts[MAXC][2]; int last_ncontacts = 0;
   long total_ticks = 0;
+  // command trace for the env-logic parity tests: events of 9 doubles {code, v[8]} (tests/golden/make_golden.py)
+  bool tracing = false; std::vector<double> trace;
+  void ev(int code, std::initializer_list<double> v) {
+    if (!tracing) return;
+    size_t at = trace.size(); trace.resize(at + 9, 0.0); trace[at] = code;
+    int k = 1; for (double x : v) if (k < 9) trace[at + k++] = x;
+  }
 
   Env(int t, uint64_t s, uint32_t g) : w(t), env_type(t), seed(s), gidx(g) {}
 
+  static bool settled(double l1_motion) { return l1_motion < BP_SETTLE_THRESHOLD; }
   int settle() {  // wait_until_stable, e.g. env_ball_balance_v0.py:94-103
     double prev[NDOF]; std::memcpy(prev, w.rob.q, sizeof(prev));
     int n = 0;
     for (; n < BP_SETTLE_MAX_TICKS;) {
       w.tick(); n++;
       double s = 0; for (int d = 0; d < NDOF; d++) s += std::fabs(prev[d] - w.rob.q[d]);
-      if (s < BP_SETTLE_THRESHOLD) break;
+      if (settled(s)) break;
       std::memcpy(prev, w.rob.q, sizeof(prev));
     }
     total_ticks += n;
+    ev(EV_SETTLE, {(double)n});
     return n;
   }
-  void move_ee_end(V3 pos, Q4 q) { double t[6]; w.ik(pos, q, t); for (int i = 0; i < 6; i++) w.target[i] = t[i]; w.arm_armed = true; }
-  void move_gripper(double len) { w.target[6] = gripper_angle(len); w.grip_armed = true; }
+  enum { EV_IK = 1, EV_GRIPPER = 2, EV_SPAWN = 3, EV_TICKS = 4, EV_SETTLE = 5, EV_JOINTS = 6, EV_RESET_ARM = 7 };
+  void move_ee_end(V3 pos, Q4 q) {
+    ev(EV_IK, {pos.x, pos.y, pos.z, q.x, q.y, q.z, q.w});
+    double t[6]; w.ik(pos, q, t);
+    for (int i = 0; i < 6; i++) w.target[i] = t[i];
+    w.arm_armed = true;
+  }
+  void move_ee_joints(const double* a) {
+    ev(EV_JOINTS, {a[0], a[1], a[2], a[3], a[4], a[5]});
+    for (int i = 0; i < 6; i++) w.target[i] = a[i];
+    w.arm_armed = true;
+  }
+  void move_gripper(double len) { w.target[6] = gripper_angle(len); w.grip_armed = true; ev(EV_GRIPPER, {w.target[6], len}); }
   void ee_pose(V3& p, Q4& q) { w.rob.fk(); p = w.rob.p[7]; q = w.rob.quat[7]; }
-  void spawn(int b, V3 pos, Q4 q) { FreeBody& B = w.fb[b]; B.pos = pos; B.quat = q; B.lin = V3(); B.ang = V3(); B.active = true; }
+  void spawn(int b, V3 pos, Q4 q) {
+    ev(EV_SPAWN, {(double)b, pos.x, pos.y, pos.z, q.x, q.y, q.z, q.w});
+    FreeBody& B = w.fb[b]; B.pos = pos; B.quat = q; B.lin = V3(); B.ang = V3(); B.active = true;
+  }
   double draw(const double* ov, int k) { return ov ? ov[k] : urand(seed, gidx, episode, (uint32_t)k); }
 
   bool touch(bool (*pred)(const ShapeDef&, const ShapeDef&, void*), void* ctx = nullptr) const {
@@ -84,7 +108,9 @@ struct Env {
     int ticks = 0;
     for (int b = 0; b < MAXFREE; b++) w.fb[b].active = false;
     for (int i = 0; i < 6; i++) { w.rob.q[i] = REST_POSE[i]; w.rob.qd[i] = 0; }   // robot.py:93-94
+    ev(EV_RESET_ARM, {REST_POSE[0], REST_POSE[1], REST_POSE[2], REST_POSE[3], REST_POSE[4], REST_POSE[5]});
     for (int i = 0; i < BP_RESET_ARM_TICKS; i++) { w.tick(); ticks++; total_ticks++; }  // robot.py:97-98
+    ev(EV_TICKS, {(double)BP_RESET_ARM_TICKS});
     move_gripper(0.085);                                                            // robot.py:100-101
     V3 ep; Q4 eq;
     switch (env_type) {
@@ -174,18 +200,38 @@ struct Env {
     }
   }
 
-  // One gym step without auto-reset. Returns settle ticks.
-  int step(const double* a, double u, double* obs, double* reward, uint8_t* terminated, uint8_t* truncated, uint8_t* success) {
+  // The part of step() before wait_until_stable: action -> motor targets. Returns the reward accrued so far.
+  double prologue(const double* a, double u) {
     V3 ep; Q4 eq;
-    double rew = 0; bool term = false, succ = false;
-    int n = 0;
+    double rew = 0;
     switch (env_type) {
       case ENV_BALL: case ENV_TWO: {
         if (env_type == ENV_TWO) for (int i = 0; i < 3; i++) rew -= std::fabs(a[i]);
         ee_pose(ep, eq);
         V3 e = euler_from_quat(eq);
         move_ee_end(ep, quat_from_euler(e.x + a[0], e.y + a[1], e.z + a[2]));
-        n = settle();
+        break;
+      }
+      case ENV_PUSH: case ENV_GOLF:
+        ee_pose(ep, eq);
+        move_ee_end(ep + V3(a[0], a[1], a[2]), vertical);
+        break;
+      case ENV_GRASP: {
+        double a0 = a[0], a1 = a[1];
+        int sel = (a0 + a1 == 0) ? (u < 0.5 ? 0 : 1) : (u * (a0 + a1) < a0 ? 0 : 1);
+        if (sel == 0) move_ee_joints(a + 2);
+        else move_gripper(a[8] < 0.5 ? 0.085 : 0.0);
+        break;
+      }
+    }
+    return rew;
+  }
+
+  // The part of step() after wait_until_stable: contact predicates, reward, termination, observation.
+  void epilogue(double rew, double* obs, double* reward, uint8_t* terminated, uint8_t* truncated, uint8_t* success) {
+    bool term = false, succ = false;
+    switch (env_type) {
+      case ENV_BALL: case ENV_TWO: {
         rew += 1;
         if (env_type == ENV_BALL) {
           term = w.fb[1].pos.z < w.fb[0].pos.z;
@@ -196,9 +242,6 @@ struct Env {
         break;
       }
       case ENV_PUSH: {
-        ee_pose(ep, eq);
-        move_ee_end(ep + V3(a[0], a[1], a[2]), vertical);
-        n = settle();
         bool table = touch([](const ShapeDef& A, const ShapeDef& B, void*) { return A.body == 0 && B.body < 0 && A.link != 0; });
         bool fingers = touch([](const ShapeDef& A, const ShapeDef& B, void*) { return A.body == 0 && B.body == 2 && A.link >= 9 && A.link <= 18; });
         if (table) { rew -= 0.01; }
@@ -213,11 +256,6 @@ struct Env {
         break;
       }
       case ENV_GRASP: {
-        double a0 = a[0], a1 = a[1];
-        int sel = (a0 + a1 == 0) ? (u < 0.5 ? 0 : 1) : (u * (a0 + a1) < a0 ? 0 : 1);
-        if (sel == 0) { for (int i = 0; i < 6; i++) w.target[i] = a[2 + i]; w.arm_armed = true; }
-        else move_gripper(a[8] < 0.5 ? 0.085 : 0.0);
-        n = settle();
         V3 gc = w.gripper_center();
         double d = norm(gc - w.fb[0].pos);
         bool l = touch([](const ShapeDef& A, const ShapeDef& B, void*) { return A.body == 0 && B.body == 1 && A.link >= 11 && A.link <= 13; });
@@ -235,9 +273,6 @@ struct Env {
         break;
       }
       case ENV_GOLF: {
-        ee_pose(ep, eq);
-        move_ee_end(ep + V3(a[0], a[1], a[2]), vertical);
-        n = settle();
         V3 hole(0, -0.6, 0.02), ball = w.fb[1].pos;
         bool in_fingers = touch([](const ShapeDef& A, const ShapeDef& B, void*) { return A.body == 0 && B.body == 1 && A.link >= 9 && A.link <= 18; });
         if (norm(hole - ball) < 0.05) { rew += 10; succ = true; term = true; }
@@ -259,6 +294,13 @@ struct Env {
     step_count++;
     *reward = rew; *terminated = term; *success = succ; *truncated = step_count >= w.sc.max_steps;
     observe(obs);
+  }
+
+  // One gym step without auto-reset. Returns settle ticks.
+  int step(const double* a, double u, double* obs, double* reward, uint8_t* terminated, uint8_t* truncated, uint8_t* success) {
+    double rew = prologue(a, u);
+    int n = settle();
+    epilogue(rew, obs, reward, terminated, truncated, success);
     return n;
   }
 
@@ -356,6 +398,69 @@ int urgo_contacts(void* h, int32_t* pairs, int32_t* count) {
   }
   return 0;
 }
+// ---- env-logic entry points (no physics): the two halves of step() around wait_until_stable, and the command trace
+// out[16] = reward so far, motor targets[7], arm_armed, grip_armed
+int urgo_prologue(void* h, int env, const double* action, double u, double* out) {
+  Env& e = ((Batch*)h)->envs[env];
+  out[0] = e.prologue(action, u);
+  for (int m = 0; m < NMOTOR; m++) out[1 + m] = e.w.target[m];
+  out[8] = e.w.arm_armed; out[9] = e.w.grip_armed;
+  return 0;
+}
+// pairs[npairs][2] = shape indices in contact after the (skipped) settle
+int urgo_epilogue(void* h, int env, double reward_so_far, int npairs, const int32_t* pairs, double* obs, double* reward, uint8_t* terminated,
+                  uint8_t* truncated, uint8_t* success) {
+  Env& e = ((Batch*)h)->envs[env];
+  e.w.contacts.clear();
+  for (int i = 0; i < npairs && i < MAXC; i++) { Contact c; c.sa = pairs[2 * i]; c.sb = pairs[2 * i + 1]; e.w.contacts.push_back(c); }
+  e.epilogue(reward_so_far, obs, reward, terminated, truncated, success);
+  return 0;
+}
+void urgo_set_trace(void* h, int on) { for (auto& e : ((Batch*)h)->envs) { e.tracing = on != 0; e.trace.clear(); } }
+int urgo_trace(void* h, int env, double* out, int max_events) {
+  Env& e = ((Batch*)h)->envs[env]; int n = (int)(e.trace.size() / 9);
+  for (int i = 0; i < n && i < max_events; i++) std::memcpy(out + 9 * i, e.trace.data() + 9 * i, sizeof(double) * 9);
+  return n;
+}
+// world-frame kinematic quantities of the current state that the env logic reads: ee pos3 quat4, link 11 pos3, link 16 pos3,
+// gripper centre3, club foot3 (Golf only)
+void urgo_kinematics(void* h, int env, double* out19) {
+  Env& e = ((Batch*)h)->envs[env]; V3 p; Q4 q; e.ee_pose(p, q);
+  double* o = out19; o[0] = p.x; o[1] = p.y; o[2] = p.z; o[3] = q.x; o[4] = q.y; o[5] = q.z; o[6] = q.w;
+  V3 a = e.w.rob.p[11], b = e.w.rob.p[16], c = e.w.gripper_center();
+  o[7] = a.x; o[8] = a.y; o[9] = a.z; o[10] = b.x; o[11] = b.y; o[12] = b.z; o[13] = c.x; o[14] = c.y; o[15] = c.z;
+  V3 f = e.env_type == ENV_GOLF ? e.club_foot() : V3(); o[16] = f.x; o[17] = f.y; o[18] = f.z;
+}
+// the settle rule alone: ticks wait_until_stable takes when the summed |joint motion| of tick k is l1[min(k, n-1)]
+int urgo_settle_count(const double* l1, int n) {
+  int k = 0;
+  for (; k < BP_SETTLE_MAX_TICKS;) { double s = l1[k < n ? k : n - 1]; k++; if (Env::settled(s)) break; }
+  return k;
+}
+// static model facts the env-logic tests compare with the reference's robot set-up
+// out: dof_link[12], effort[12], velocity[12], lower[12], upper[12], gear_child_link[5], gear_ratio[5], rest_pose[6],
+//      reset_arm_ticks, settle_max_ticks, settle_threshold, club_zc, ik_iters  (= 75 doubles)
+void urgo_model_info(double* o) {
+  int k = 0, dof_link[NDOF], nd = 0;
+  for (int i = 0; i < URG_NLINK; i++) if (URG_LINKS[i].jtype == 1) dof_link[nd++] = i;
+  for (int d = 0; d < NDOF; d++) o[k++] = dof_link[d];
+  for (int d = 0; d < NDOF; d++) o[k++] = URG_LINKS[dof_link[d]].effort;
+  for (int d = 0; d < NDOF; d++) o[k++] = URG_LINKS[dof_link[d]].velocity;
+  for (int d = 0; d < NDOF; d++) o[k++] = URG_LINKS[dof_link[d]].lower;
+  for (int d = 0; d < NDOF; d++) o[k++] = URG_LINKS[dof_link[d]].upper;
+  for (int g = 0; g < 5; g++) o[k++] = dof_link[GEAR_DOF[g]];
+  for (int g = 0; g < 5; g++) o[k++] = GEAR_RATIO[g];
+  for (int i = 0; i < 6; i++) o[k++] = REST_POSE[i];
+  o[k++] = BP_RESET_ARM_TICKS; o[k++] = BP_SETTLE_MAX_TICKS; o[k++] = BP_SETTLE_THRESHOLD; o[k++] = CLUB_ZC; o[k++] = BP_IK_ITERS;
+}
+// scene facts: out[0]=gravity z, out[1..3]=free-body masses; per shape (urgo_shape_detail): kind (0 box, 1 sphere),
+// half3 or radius, local centre3, mu, restitution, rolling friction
+void urgo_scene_info(int t, double* out4) { Scene s = make_scene(t); out4[0] = s.gravity; for (int b = 0; b < MAXFREE; b++) out4[1 + b] = b < s.nfree ? s.fmass[b] : 0.0; }
+void urgo_shape_detail(int t, int idx, double* o) {
+  Scene s = make_scene(t); const ShapeDef& d = s.shapes[idx];
+  o[0] = d.kind; o[1] = d.kind == 0 ? d.half.x : d.radius; o[2] = d.half.y; o[3] = d.half.z; o[4] = d.lc.x; o[5] = d.lc.y; o[6] = d.lc.z;
+  o[7] = d.mu; o[8] = d.rest; o[9] = d.roll;
+}
 long urgo_total_ticks(void* h) { long s = 0; for (auto& e : ((Batch*)h)->envs) s += e.total_ticks; return s; }
 
 // ---- unit-level entry points for parity tests
@@ -375,7 +480,9 @@ void urgo_tick_stats(void* h, long* out5) {
   for (auto& e : ((Batch*)h)->envs) { out5[0] += e.w.st_ticks; out5[1] += e.w.st_iters; out5[2] += e.w.st_rows; out5[3] += e.w.st_contacts; out5[4] += e.w.st_rowiters; }
 }
 void urgo_tick_hist(void* h, long* rows96, long* nc24, long* nnc32) {
-  for (int k = 0; k < 96; k++) rows96[k] = 0; for (int k = 0; k < 24; k++) nc24[k] = 0; for (int k = 0; k < 32; k++) nnc32[k] = 0;
+  for (int k = 0; k < 96; k++) rows96[k] = 0;
+  for (int k = 0; k < 24; k++) nc24[k] = 0;
+  for (int k = 0; k < 32; k++) nnc32[k] = 0;
   for (auto& e : ((Batch*)h)->envs) { for (int k = 0; k < 96; k++) rows96[k] += e.w.st_hist_rows[k]; for (int k = 0; k < 24; k++) nc24[k] += e.w.st_hist_nc[k]; for (int k = 0; k < 32; k++) nnc32[k] += e.w.st_hist_nnc[k]; }
 }
 int urgo_last_iters(void* h, int env) { return ((Batch*)h)->envs[env].w.last_iters; }

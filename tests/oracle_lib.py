@@ -27,7 +27,8 @@ def lib():
         L.urgo_create.argtypes = [C.c_int, C.c_int, C.c_uint64, C.c_int]
         L.urgo_destroy.argtypes = [C.c_void_p]
         for f in ('urgo_reset', 'urgo_step', 'urgo_get_state', 'urgo_set_state', 'urgo_contacts', 'urgo_tick',
-                  'urgo_last_contacts_detail', 'urgo_last_iters', 'urgo_reset_range', 'urgo_step_range'):
+                  'urgo_last_contacts_detail', 'urgo_last_iters', 'urgo_reset_range', 'urgo_step_range', 'urgo_prologue',
+                  'urgo_epilogue', 'urgo_trace'):
             getattr(L, f).restype = C.c_int
         L.urgo_total_ticks.restype = C.c_long
         L.urgo_total_ticks.argtypes = [C.c_void_p]
@@ -109,6 +110,36 @@ class OracleBatch:
     def total_ticks(self):
         return self.L.urgo_total_ticks(self.h)
 
+    # ---- env logic without physics (tests/test_reference_env_logic.py)
+    def prologue(self, action, u=0.0, env=0):
+        a = _d(action); out = np.zeros(16)
+        self.L.urgo_prologue(self.h, env, _p(a), C.c_double(u), _p(out))
+        return dict(reward=out[0], targets=out[1:8].copy(), arm_armed=bool(out[8]), grip_armed=bool(out[9]))
+
+    def epilogue(self, pairs, reward_so_far=0.0, env=0):
+        pr = np.ascontiguousarray(np.asarray(pairs, dtype=np.int32).reshape(-1, 2))
+        obs = np.zeros(self.od); rew = np.zeros(1)
+        f = np.zeros(3, np.uint8)
+        self.L.urgo_epilogue(self.h, env, C.c_double(reward_so_far), len(pr), _p(pr), _p(obs), _p(rew), _p(f[0:1]), _p(f[1:2]), _p(f[2:3]))
+        return dict(obs=obs, reward=float(rew[0]), terminated=bool(f[0]), truncated=bool(f[1]), success=bool(f[2]))
+
+    def set_trace(self, on=True):
+        self.L.urgo_set_trace(self.h, int(on))
+
+    def trace(self, env=0):
+        out = np.zeros((256, 9)); n = self.L.urgo_trace(self.h, env, _p(out), 256); return out[:n]
+
+    def kinematics(self, env=0):
+        o = np.zeros(19); self.L.urgo_kinematics(self.h, env, _p(o))
+        return dict(ee=o[0:7].copy(), link11=o[7:10].copy(), link16=o[10:13].copy(), gripper_center=o[13:16].copy(), club_foot=o[16:19].copy())
+
+    def shape_table(self):
+        """[(body, link)] per shape index: body 0 robot, k>0 free body k-1 (link -1 = its base), <0 static (link = which)."""
+        out = []
+        for i in range(self.L.urgo_num_shapes(self.t)):
+            b, l = C.c_int(), C.c_int(); self.L.urgo_shape_info(self.t, i, C.byref(b), C.byref(l)); out.append((b.value, l.value))
+        return out
+
 
 def fk(q):
     out = np.zeros((19, 7)); q = _d(q); lib().urgo_fk(_p(q), _p(out)); return out
@@ -140,3 +171,29 @@ def quat_from_euler(e):
 
 def box_box(a, b, margin):
     out = np.zeros((4, 10)); a = _d(a); b = _d(b); n = lib().urgo_box_box(_p(a), _p(b), margin, _p(out)); return out[:n]
+
+
+def settle_count(l1_motion_per_tick):
+    a = _d(l1_motion_per_tick); L = lib(); L.urgo_settle_count.restype = C.c_int
+    return L.urgo_settle_count(_p(a), len(a))
+
+
+def model_facts():
+    """Static facts of the oracle's robot / env model (see urgo_model_info in oracle/urgo_env.cpp)."""
+    o = np.zeros(81); lib().urgo_model_info(_p(o))
+    return dict(dof_link=o[0:12].astype(int).tolist(), effort=o[12:24].tolist(), velocity=o[24:36].tolist(), lower=o[36:48].tolist(),
+                upper=o[48:60].tolist(), gear_child_link=o[60:65].astype(int).tolist(), gear_ratio=o[65:70].tolist(),
+                rest_pose=o[70:76].tolist(), reset_arm_ticks=int(o[76]), settle_max_ticks=int(o[77]), settle_threshold=float(o[78]),
+                club_zc=float(o[79]), ik_iters=int(o[80]))
+
+
+def scene_facts(env):
+    t = ENV_TYPES[env] if isinstance(env, str) else int(env)
+    L = lib(); o = np.zeros(4); L.urgo_scene_info(t, _p(o))
+    shapes = []
+    for i in range(L.urgo_num_shapes(t)):
+        b, l = C.c_int(), C.c_int(); L.urgo_shape_info(t, i, C.byref(b), C.byref(l))
+        d = np.zeros(10); L.urgo_shape_detail(t, i, _p(d))
+        shapes.append(dict(body=b.value, link=l.value, kind='box' if d[0] == 0 else 'sphere', half=d[1:4].tolist(), radius=float(d[1]),
+                           centre=d[4:7].tolist(), mu=float(d[7]), restitution=float(d[8]), rolling=float(d[9])))
+    return dict(gravity=float(o[0]), masses=o[1:4].tolist(), shapes=shapes)
