@@ -78,6 +78,16 @@ int urgym_set_state(urgym_handle h, const float* state_dev, void* stream);
  * pairs_dev int32[N,URGYM_MAX_CONTACTS,2] (-1 padded), count_dev int32[N]. */
 int urgym_contacts(urgym_handle h, int32_t* pairs_dev, int32_t* count_dev, void* stream);
 
+/* Env-logic check entry: step() with the physics skipped. Runs the part of step() before wait_until_stable (action ->
+ * IK / motor targets, written to the state record) and the part after it (contact predicates, reward, termination,
+ * success, observation, step counter) on the CURRENT state, with the contact set the predicates see given by the caller
+ * as shape-index pairs (pairs_dev int32[N,URGYM_MAX_CONTACTS,2], count_dev int32[N]) instead of produced by the
+ * simulation. Exists so that the device env logic can be compared case by case with fixtures recorded from the
+ * reference's own step() (tests/golden/reference_env_logic.json: env_*_v0.py step() and its predicates). */
+int urgym_step_logic(urgym_handle h, const float* action_dev, const float* u_dev, const int32_t* pairs_dev, const int32_t* count_dev,
+                     float* obs_dev, float* reward_dev, uint8_t* terminated_dev, uint8_t* truncated_dev, uint8_t* success_dev,
+                     void* stream);
+
 /* Raw stepSimulation: `nticks` physics ticks on every env with the current motor targets, no env logic. */
 int urgym_tick(urgym_handle h, int nticks, void* stream);
 

@@ -1,0 +1,351 @@
+"""Parity of the CUDA path (through the C ABI) with the CPU oracle and with the reference-recorded fixtures. B200 only.
+
+Bars (fp32 device arithmetic against the fp64 oracle; tolerances stated at each assert):
+  * kinematics (FK / IK / gripper centre): <= 1e-5 absolute.
+  * reset(): tick counts EXACT, first observation <= 1e-4.
+  * one physics tick from an identical state: positions <= 2e-5, velocities <= 2e-3 (one fp32 PGS solve).
+  * one gym step from an identical state (re-synchronised every step so that chaotic growth does not accumulate):
+    the settle-loop trip count is an integer decision on a 5e-3 threshold — it must agree on >= 80% of (env, step)
+    pairs, and where it agrees observations agree to 5e-3, rewards to 5e-3, flags and contact-pair sets exactly
+    on >= 95%.
+  * env logic (commands, predicates, reward, termination, observation) against tests/golden/reference_env_logic.json,
+    i.e. against the reference's own step(): obs <= 2e-5, reward <= 2e-4, flags exact (fixture cases that sit exactly
+    on a threshold are excluded — fp32 may land on either side).
+  * full-size runs (4096 / 16384 envs): finite, unit quaternions, episode accounting, time-limit truncation,
+    layout independence (bit-exact), host-buffer entry == device entry (bit-exact).
+"""
+import json
+import os
+
+import numpy as np
+import pytest
+import torch
+
+import oracle_lib as O
+
+pytestmark = pytest.mark.gpu
+ENVS = ['BallBalance', 'TwoBallsBalance', 'CubesPush', 'CubesGrasp', 'Golf']
+OUT = os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), 'gpurun_out')
+
+
+@pytest.fixture(scope='module', autouse=True)
+def _need_gpu(built):
+    if not torch.cuda.is_available():
+        pytest.fail('no CUDA device: the gpu tests must run on the B200 box')
+    return True
+
+
+def _batch(*a, **k):
+    from urgym_b200.batch import EnvBatch
+    return EnvBatch(*a, **k)
+
+
+def _np(t):
+    return t.detach().cpu().numpy()
+
+
+def _actions(rng, name, n):
+    if name == 'CubesGrasp':
+        return np.concatenate([rng.uniform(0, 1, (n, 2)), rng.uniform(-1, 1, (n, 6)), rng.uniform(0, 1, (n, 1))], 1).astype(np.float32).astype(np.float64)
+    return rng.uniform(-0.1, 0.1, (n, 3)).astype(np.float32).astype(np.float64)
+
+
+def _record(name, payload):
+    try:
+        os.makedirs(OUT, exist_ok=True)
+        with open(os.path.join(OUT, 'parity_metrics.jsonl'), 'a') as f:
+            f.write(json.dumps(dict(test=name, **payload)) + '\n')
+    except OSError:
+        pass
+
+
+# ------------------------------------------------------------------------------------------------ kinematics
+def test_kinematics_match_oracle():
+    from urgym_b200.batch import forward_kinematics, gripper_center, inverse_kinematics
+    rng = np.random.default_rng(0)
+    q = rng.uniform(-1.5, 1.5, (256, 12)); q[:, 6:] = rng.uniform(0, 0.8, (256, 1)) * np.array([1, -1, 1, 1, -1, 1])
+    q = q.astype(np.float32).astype(np.float64)
+    fk_g = _np(forward_kinematics(q)).astype(np.float64)
+    fk_o = np.stack([O.fk(x) for x in q])
+    assert np.abs(fk_g[..., :3] - fk_o[..., :3]).max() < 1e-5
+    assert np.abs(fk_g[..., 3:] - fk_o[..., 3:]).max() < 1e-5                      # same sign convention too
+    tg = fk_o[:, 7].copy(); tg[:, :3] += rng.uniform(-0.1, 0.1, (256, 3)); tg = tg.astype(np.float32).astype(np.float64)
+    ik_g = _np(inverse_kinematics(q, tg)); ik_o = np.stack([O.ik(q[i], tg[i]) for i in range(256)])
+    assert np.abs(ik_g - ik_o).max() < 1e-5
+    gc_g = _np(gripper_center(q)); gc_o = np.stack([O.gripper_center(x) for x in q])
+    assert np.abs(gc_g - gc_o).max() < 1e-5
+
+
+# ------------------------------------------------------------------------------------------- reset / tick / step
+@pytest.mark.parametrize('name', ENVS)
+def test_reset_ticks_exact_and_first_observation(name):
+    n = 32
+    ob, gb = O.OracleBatch(name, n, seed=3), _batch(name, n, seed=3)
+    oo, ont = ob.reset()
+    go = _np(gb.reset())
+    np.testing.assert_array_equal(_np(gb.reset_ticks), ont)
+    err = np.abs(go - oo).max()
+    _record('reset', dict(env=name, obs_err=float(err)))
+    assert err < 1e-4
+    # seeded draws come from the same counter-based generator on both sides: the randomised spawn coordinates agree
+    assert np.isfinite(go).all()
+
+
+@pytest.mark.parametrize('name', ENVS)
+def test_single_tick_from_identical_state(name):
+    n = 16
+    ob, gb = O.OracleBatch(name, n, seed=5), _batch(name, n, seed=5)
+    ob.reset()
+    rng = np.random.default_rng(1)
+    ob.step(_actions(rng, name, n), u=rng.uniform(0, 1, n))                          # a state with contacts and motion
+    s0 = ob.get_state().astype(np.float32)
+    gb.set_state(torch.tensor(s0)); ob.set_state(s0.astype(np.float64))
+    ob.tick(1); gb.tick(1)
+    so, sg = ob.get_state(), _np(gb.get_state()).astype(np.float64)
+    pos = list(range(0, 12)) + [38 + 13 * b + k for b in range(3) for k in range(7)]
+    vel = list(range(12, 24)) + [38 + 13 * b + k for b in range(3) for k in range(7, 13)]
+    ep, ev = np.abs(sg[:, pos] - so[:, pos]).max(), np.abs(sg[:, vel] - so[:, vel]).max()
+    _record('single_tick', dict(env=name, pos_err=float(ep), vel_err=float(ev)))
+    assert ep < 2e-5 and ev < 2e-3
+
+
+@pytest.mark.parametrize('name', ENVS)
+def test_resynchronised_steps_match_oracle(name):
+    n, steps = 32, 6
+    ob, gb = O.OracleBatch(name, n, seed=7), _batch(name, n, seed=7)
+    ob.reset(); gb.reset()
+    rng = np.random.default_rng(2)
+    same_ticks = total = flags_ok = contacts_ok = 0
+    obs_err, rew_err = [], []
+    for k in range(steps):
+        s = ob.get_state().astype(np.float32)
+        gb.set_state(torch.tensor(s)); ob.set_state(s.astype(np.float64))
+        a, u = _actions(rng, name, n), rng.uniform(0, 1, n).astype(np.float32).astype(np.float64)
+        ro = ob.step(a, u=u)
+        gb.step(a, u=u, autoreset=False)
+        po, co = ob.contacts(); pg, cg = gb.contacts()
+        pg, cg = _np(pg), _np(cg)
+        nt_g, obs_g, rew_g = _np(gb.nticks)[:, 0], _np(gb.obs), _np(gb.reward)
+        tg, sg = _np(gb.terminated).astype(bool), _np(gb.success).astype(bool)
+        for i in range(n):
+            total += 1
+            if nt_g[i] != ro['nticks'][i, 0]:
+                continue
+            same_ticks += 1
+            obs_err.append(np.abs(obs_g[i] - ro['obs'][i]).max()); rew_err.append(abs(rew_g[i] - ro['reward'][i]))
+            flags_ok += int(tg[i] == ro['terminated'][i] and sg[i] == ro['success'][i])
+            so_ = {tuple(p) for p in po[i, :co[i]].tolist()}; sg_ = {tuple(p) for p in pg[i, :cg[i]].tolist()}
+            contacts_ok += int(so_ == sg_)
+        # episodes that ended are restarted on the oracle so that the next round starts from live states
+        done = ro['terminated'] | ro['truncated']
+        if done.any():
+            ob.reset(mask=done)
+    m = dict(env=name, same_ticks=same_ticks / total, obs_err_p50=float(np.median(obs_err)), obs_err_p95=float(np.quantile(obs_err, 0.95)),
+             obs_err_max=float(np.max(obs_err)), rew_err_max=float(np.max(rew_err)), flags_ok=flags_ok / same_ticks, contacts_ok=contacts_ok / same_ticks)
+    _record('resync_steps', m)
+    assert m['same_ticks'] >= 0.80, m
+    assert m['obs_err_p95'] < 5e-3 and m['flags_ok'] >= 0.95 and m['contacts_ok'] >= 0.95, m
+    assert np.quantile(rew_err, 0.95) < 5e-3, m
+
+
+# ------------------------------------------------------------------------------- env logic vs the reference fixture
+GOLD = json.load(open(os.path.join(os.path.dirname(__file__), 'golden', 'reference_env_logic.json')))
+ON_THRESHOLD = ('exactly', '_at_', 'level_with', 'unit_distance')
+
+
+@pytest.mark.parametrize('name', ENVS)
+@pytest.mark.parametrize('reward_type', ['dense', 'sparse'])
+def test_env_logic_matches_reference_fixture(name, reward_type):
+    from test_reference_env_logic import _oracle_pairs
+    cases = [c for c in GOLD['envs'][name]['step'] if c['reward_type'] == reward_type and 'raises' not in c
+             and not any(t in c['label'] for t in ON_THRESHOLD)]
+    if not cases:
+        pytest.skip('no %s cases for %s' % (reward_type, name))
+    n = len(cases)
+    gb = _batch(name, n, seed=1, reward_sparse=(reward_type == 'sparse'))
+    gb.reset()
+    table = O.OracleBatch(name, 1).shape_table()
+    st = np.zeros((n, 96), np.float32); acts = np.zeros((n, gb.act_dim), np.float32); us = np.zeros(n, np.float32)
+    pairs = -np.ones((n, 16, 2), np.int32); counts = np.zeros(n, np.int32)
+    for i, c in enumerate(cases):
+        st[i, :len(c['state'])] = c['state']; acts[i] = c['action']; us[i] = c['u']
+        pr = _oracle_pairs(table, c['contacts'])
+        counts[i] = len(pr)
+        for k, p in enumerate(pr):
+            pairs[i, k] = p
+    gb.set_state(torch.tensor(st))
+    obs, rew, term, trunc, succ = gb.step_logic(acts, pairs, counts, u=us)
+    obs, rew, term, succ = _np(obs), _np(rew), _np(term).astype(bool), _np(succ).astype(bool)
+    after = _np(gb.get_state())
+    bad = []
+    for i, c in enumerate(cases):
+        e_obs = np.abs(obs[i] - np.array(c['obs'])).max()
+        e_rew = abs(rew[i] - c['reward'])
+        ok = e_obs < 2e-5 and e_rew < 2e-4 and term[i] == c['terminated'] and succ[i] == bool(c['info'].get('is_success', False))
+        cmd = c['commands'][0]
+        if cmd['op'] == 'ik':      # the commanded joint targets are the IK solution for the reference's target pose
+            want = O.ik(st[i, :12].astype(np.float64), np.array(cmd['pos'] + cmd['orn']))
+            ok = ok and np.abs(after[i, 24:30] - want).max() < 1e-4
+        elif cmd['op'] == 'joints':
+            ok = ok and np.array_equal(after[i, 24:30], np.array(cmd['targets'], np.float32))
+        else:
+            ok = ok and abs(after[i, 30] - cmd['target']) < 1e-6
+        if name == 'CubesGrasp':
+            fl = int(after[i, 31])
+            ok = ok and {'approached': bool(fl & 4), 'grasped': bool(fl & 8)} == c['subgoals_after']
+        if not ok:
+            bad.append((i, c['label'], c['contacts'], float(e_obs), float(e_rew), bool(term[i]), c['terminated']))
+    _record('env_logic', dict(env=name, reward_type=reward_type, cases=n, bad=len(bad)))
+    assert not bad, bad[:5]
+
+
+# ------------------------------------------------------------------------------------------ full-size properties
+@pytest.mark.parametrize('name,n', [('BallBalance', 4096), ('CubesGrasp', 16384), ('Golf', 4096)])
+def test_full_size_run_properties(name, n):
+    gb = _batch(name, n, seed=11)
+    gb.reset()
+    assert int(_np(gb.reset_ticks).min()) >= 11
+    rng = np.random.default_rng(3)
+    steps = 22 if name == 'CubesGrasp' else 8
+    ended = 0; tick_sum = int(_np(gb.reset_ticks).astype(np.int64).sum())
+    restarted_early = torch.zeros(n, dtype=torch.bool, device=gb.device)
+    for k in range(steps):
+        a = torch.tensor(_actions(rng, name, n), dtype=torch.float32, device=gb.device)
+        obs, rew, term, trunc, succ = gb.step(a, autoreset=True)
+        assert torch.isfinite(obs).all() and torch.isfinite(rew).all()
+        done = (term | trunc).bool()
+        ended += int(done.sum()); tick_sum += int(gb.nticks.to(torch.int64).sum())
+        assert not (succ.bool() & ~term.bool()).any()                                   # success implies termination
+        nt = gb.nticks[:, 0]
+        assert int(nt.min()) >= 1 and int(nt.max()) <= 480
+        assert ((gb.nticks[:, 1] > 0) == done).all()                                    # reset ticks only where an episode ended
+        if name == 'CubesGrasp' and k < 19:
+            restarted_early |= done
+        if name == 'CubesGrasp' and k == 19:
+            assert trunc.bool()[~restarted_early].all()                                 # TimeLimit: 20 steps
+    st = gb.get_state()
+    assert torch.isfinite(st).all()
+    fl = st[:, 31].to(torch.int64)
+    for b in range(3):
+        act = (fl & (16 << b)) != 0
+        if act.any():
+            qn = st[act][:, 41 + 13 * b: 45 + 13 * b].norm(dim=1)
+            assert (qn - 1).abs().max() < 1e-4
+    assert (st[:, 32] >= 0).all() and (st[:, 32] < gb.max_episode_steps).all()
+    stats = gb.stats()
+    assert stats['episodes'] == ended and stats['env_steps'] == steps * n and stats['ticks'] == tick_sum
+    assert stats['length_sum'] >= stats['episodes']
+
+
+@pytest.mark.parametrize('name', ['BallBalance', 'CubesPush'])
+def test_shard_layout_is_bit_exact(name):
+    whole, part = _batch(name, 64, seed=13), _batch(name, 32, seed=13, env_index_offset=32)
+    np.testing.assert_array_equal(_np(whole.reset())[32:], _np(part.reset()))
+    rng = np.random.default_rng(4)
+    for _ in range(3):
+        a = _actions(rng, name, 64)
+        whole.step(a, autoreset=True); part.step(a[32:], autoreset=True)
+        np.testing.assert_array_equal(_np(whole.obs)[32:], _np(part.obs))
+        np.testing.assert_array_equal(_np(whole.nticks)[32:], _np(part.nticks))
+    np.testing.assert_array_equal(_np(whole.get_state())[32:], _np(part.get_state()))
+
+
+def test_host_entry_equals_device_entry():
+    import ctypes as C
+    from urgym_b200 import _lib
+    n = 48
+    a_dev, a_host = _batch('CubesPush', n, seed=2), _batch('CubesPush', n, seed=2)
+    a_dev.reset(); a_host.reset()
+    L = _lib.lib()
+    rng = np.random.default_rng(6)
+    for _ in range(3):
+        act = _actions(rng, 'CubesPush', n).astype(np.float32)
+        a_dev.step(act, autoreset=True)
+        obs = np.zeros((n, 9), np.float32); rew = np.zeros(n, np.float32); fin = np.zeros((n, 9), np.float32)
+        t, tr, su = (np.zeros(n, np.uint8) for _ in range(3)); nt = np.zeros((n, 2), np.int32)
+        p = lambda x: x.ctypes.data_as(C.c_void_p)
+        _lib.check(L.urgym_step_host(a_host.h, p(act), None, None, p(obs), p(rew), p(t), p(tr), p(su), p(fin), p(nt), 1))
+        np.testing.assert_array_equal(obs, _np(a_dev.obs)); np.testing.assert_array_equal(rew, _np(a_dev.reward))
+        np.testing.assert_array_equal(nt, _np(a_dev.nticks)); np.testing.assert_array_equal(t, _np(a_dev.terminated))
+
+
+def test_state_round_trip_and_masked_reset():
+    gb = _batch('TwoBallsBalance', 16, seed=8)
+    gb.reset()
+    s = gb.get_state().clone()
+    gb.set_state(s)
+    assert torch.equal(gb.get_state(), s)
+    obs_before = gb.obs.clone()
+    mask = torch.zeros(16, dtype=torch.uint8); mask[::4] = 1
+    gb.reset(mask=mask)
+    s2 = gb.get_state()
+    keep = ~mask.bool().to(s.device)
+    assert torch.equal(s2[keep], s[keep]) and torch.equal(gb.obs[keep], obs_before[keep])
+    assert (s2[~keep][:, 33] == s[~keep][:, 33] + 1).all()                              # a new episode where asked
+
+
+def test_determinism_across_runs():
+    outs = []
+    for _ in range(2):
+        gb = _batch('Golf', 64, seed=21)
+        gb.reset()
+        rng = np.random.default_rng(9)
+        for _ in range(3):
+            gb.step(_actions(rng, 'Golf', 64), autoreset=True)
+        outs.append((_np(gb.obs).copy(), _np(gb.get_state()).copy()))
+    np.testing.assert_array_equal(outs[0][0], outs[1][0]); np.testing.assert_array_equal(outs[0][1], outs[1][1])
+
+
+@pytest.mark.parametrize('name', ['BallBalance', 'CubesGrasp'])
+def test_distributional_agreement_over_episodes(name):
+    """Free-running (no re-synchronisation) rollouts diverge trajectory by trajectory — the dynamics are chaotic — but
+    the statistics a learner sees must agree: mean settle ticks per step within 5%, termination rate within 0.05."""
+    from concurrent.futures import ThreadPoolExecutor
+    n, steps = 256, 24
+    ob, gb = O.OracleBatch(name, n, seed=31), _batch(name, n, seed=31)
+    rng = np.random.default_rng(10)
+    acts = [_actions(rng, name, n) for _ in range(steps)]
+    us = [rng.uniform(0, 1, n).astype(np.float32).astype(np.float64) for _ in range(steps)]
+    gb.reset()
+    nthr = min(16, os.cpu_count() or 1)
+    cuts = np.linspace(0, n, nthr + 1).astype(int)
+    with ThreadPoolExecutor(nthr) as ex:
+        list(ex.map(lambda i: ob.reset(lo=int(cuts[i]), hi=int(cuts[i + 1])), range(nthr)))
+        t_o = t_g = d_o = d_g = 0
+        for k in range(steps):
+            res = list(ex.map(lambda i: ob.step(acts[k], u=us[k], autoreset=True, lo=int(cuts[i]), hi=int(cuts[i + 1])), range(nthr)))
+            for i, r in enumerate(res):
+                sl = slice(int(cuts[i]), int(cuts[i + 1]))
+                t_o += int(r['nticks'][sl, 0].sum()); d_o += int((r['terminated'][sl] | r['truncated'][sl]).sum())
+            gb.step(acts[k], u=us[k], autoreset=True)
+            t_g += int(gb.nticks[:, 0].sum()); d_g += int((gb.terminated | gb.truncated).bool().sum())
+    m = dict(env=name, ticks_per_step_oracle=t_o / (n * steps), ticks_per_step_gpu=t_g / (n * steps), done_rate_oracle=d_o / (n * steps), done_rate_gpu=d_g / (n * steps))
+    _record('distribution', m)
+    assert abs(m['ticks_per_step_gpu'] / m['ticks_per_step_oracle'] - 1) < 0.05, m
+    assert abs(m['done_rate_gpu'] - m['done_rate_oracle']) < 0.05, m
+
+
+# ------------------------------------------------------------------------------------------------- gym-style API
+def test_vector_env_and_single_env_api():
+    from urgym_b200 import envs as E
+    v = E.URGymVectorEnv('URGym/CubesGrasp-v0', 128, seed=1)
+    obs, info = v.reset()
+    assert obs.shape == (128, 17) and obs.is_cuda and 'reset_ticks' in info
+    for k in range(20):
+        a = torch.rand(128, 9, device=obs.device)
+        obs, rew, term, trunc, info = v.step(a)
+    assert trunc.dtype == torch.bool and (term | trunc).all()                       # TimeLimit of 20 reached on every env
+    assert info['final_observation'].shape == obs.shape and info['is_success'].dtype == torch.bool
+    st = v.episode_statistics()
+    assert st['episodes'] >= 128 and st['env_steps'] == 20 * 128
+    v.close()
+    e = E.make('URGym/CubesPush-v0', render_mode='train')
+    o, inf = e.reset()
+    assert o.dtype == np.float64 and o.shape == (9,) and inf == {} and e.observation_space.contains(np.clip(o, -1, 1))
+    for k in range(50):
+        o, r, term, trunc, inf = e.step(e.action_space.sample())
+        assert isinstance(r, float) and isinstance(term, bool) and 'is_success' in inf
+        if term or trunc:
+            break
+    assert k == 49 and trunc or term
+    e.close()

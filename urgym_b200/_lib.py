@@ -40,6 +40,7 @@ def lib():
     L.urgym_set_state.argtypes = [vp, vp, vp]
     L.urgym_contacts.argtypes = [vp, vp, vp, vp]
     L.urgym_tick.argtypes = [vp, i32, vp]
+    L.urgym_step_logic.argtypes = [vp] + [vp] * 10
     L.urgym_fk.argtypes = [i32, i32, vp, vp, vp]
     L.urgym_ik.argtypes = [i32, i32, vp, vp, vp, vp]
     L.urgym_gripper_center.argtypes = [i32, i32, vp, vp, vp]

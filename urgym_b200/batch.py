@@ -77,6 +77,17 @@ class EnvBatch:
                                 _ptr(self.truncated), _ptr(self.success), _ptr(self.final_obs), _ptr(self.nticks), int(autoreset), _stream(d)))
         return self.obs, self.reward, self.terminated, self.truncated, self.success
 
+    def step_logic(self, action, pairs, counts, u=None):
+        """step() with the physics skipped and the contact set given (include/urgym_b200.h: urgym_step_logic)."""
+        d = self.device
+        a = _f32(action, d, (self.num_envs, self.act_dim))
+        uu = _f32(u, d, (self.num_envs,))
+        pr = torch.as_tensor(pairs, dtype=torch.int32, device=d).reshape(self.num_envs, MAX_CONTACTS, 2).contiguous()
+        cn = torch.as_tensor(counts, dtype=torch.int32, device=d).reshape(self.num_envs).contiguous()
+        check(self.L.urgym_step_logic(self.h, _ptr(a), _ptr(uu), _ptr(pr), _ptr(cn), _ptr(self.obs), _ptr(self.reward), _ptr(self.terminated),
+                                      _ptr(self.truncated), _ptr(self.success), _stream(d)))
+        return self.obs, self.reward, self.terminated, self.truncated, self.success
+
     def tick(self, n=1):
         check(self.L.urgym_tick(self.h, int(n), _stream(self.device)))
 

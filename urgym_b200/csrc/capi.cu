@@ -172,6 +172,16 @@ int urgym_step(urgym_handle h, const float* action_dev, const float* u_dev, cons
   return launch(h, P, stream);
 }
 
+int urgym_step_logic(urgym_handle h, const float* action_dev, const float* u_dev, const int32_t* pairs_dev, const int32_t* count_dev,
+                     float* obs_dev, float* reward_dev, uint8_t* terminated_dev, uint8_t* truncated_dev, uint8_t* success_dev, void* stream) {
+  if (!h || !action_dev || !pairs_dev || !count_dev || !obs_dev || !reward_dev || !terminated_dev || !truncated_dev || !success_dev)
+    return fail(URGYM_E_ARG, "urgym_step_logic: null argument");
+  KParams P; std::memset(&P, 0, sizeof(P));
+  P.mode = MODE_STEP; P.action = action_dev; P.u = u_dev; P.obs = obs_dev; P.reward = reward_dev;
+  P.term = terminated_dev; P.trunc = truncated_dev; P.succ = success_dev; P.inject_pairs = pairs_dev; P.inject_count = count_dev;
+  return launch(h, P, stream);
+}
+
 int urgym_tick(urgym_handle h, int nticks, void* stream) {
   if (!h || nticks <= 0) return fail(URGYM_E_ARG, "urgym_tick: bad arguments");
   KParams P; std::memset(&P, 0, sizeof(P));

@@ -9,6 +9,7 @@ struct KParams {
   const float* action; const float* u; const float* draws; const uint8_t* mask;
   float* obs; float* reward; uint8_t* term; uint8_t* trunc; uint8_t* succ; float* final_obs; int32_t* nticks;
   int32_t* contacts; int32_t* ccount; double* stats;
+  const int32_t* inject_pairs; const int32_t* inject_count;  // urgym_step_logic only: contact set instead of physics
   unsigned long long seed; int gidx0; int autoreset; int mode; int raw_ticks; int sparse;
 };
 enum { MODE_STEP = 0, MODE_RESET = 1, MODE_TICKS = 2 };

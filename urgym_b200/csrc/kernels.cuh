@@ -104,7 +104,16 @@ __global__ void __launch_bounds__(32) env_kernel(KParams P) {
   // ---- the tick loop
   for (;;) {
     int iters;
-    float moved = tick<G, RC>(s, M, gp, &iters);
+    float moved = 0.f;
+    if (P.inject_pairs) {  // urgym_step_logic: no physics, the caller names the contact set the predicates see
+      gp.sync();
+      const int nc = min(P.inject_count[env], UG_MAXC);
+      if (lane < nc) s.con[lane].shapes = P.inject_pairs[((size_t)env * UG_MAXC + lane) * 2] | (P.inject_pairs[((size_t)env * UG_MAXC + lane) * 2 + 1] << 8);
+      if (lane == 0) s.ncon = nc;
+      gp.sync();
+    } else {
+      moved = tick<G, RC>(s, M, gp, &iters);
+    }
     n++; tick_total++;
     bool done = phase == PH_ARM10 || phase == PH_RAW ? n >= limit : (moved < UGP_SETTLE_THRESHOLD || n >= limit);
     if (!done) continue;
