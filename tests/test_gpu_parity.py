@@ -13,6 +13,7 @@ Bars (fp32 device arithmetic against the fp64 oracle; tolerances stated at each 
   * env logic (commands, predicates, reward, termination, observation) against tests/golden/reference_env_logic.json,
     i.e. against the reference's own step(): obs <= 2e-5, reward <= 2e-4, flags exact (fixture cases that sit exactly
     on a threshold are excluded — fp32 may land on either side).
+  * >= 1e4 episodes per side under one random policy: mean return / length / success rate within 4 standard errors.
   * full-size runs (4096 / 16384 envs): finite, unit quaternions, episode accounting, time-limit truncation,
     layout independence (bit-exact), host-buffer entry == device entry (bit-exact).
 """
@@ -114,7 +115,7 @@ def test_single_tick_from_identical_state(name):
 
 @pytest.mark.parametrize('name', ENVS)
 def test_resynchronised_steps_match_oracle(name):
-    n, steps = 32, 6
+    n, steps = 32, 50          # the north star's 50-step horizon, re-synchronised every step
     ob, gb = O.OracleBatch(name, n, seed=7), _batch(name, n, seed=7)
     ob.reset(); gb.reset()
     rng = np.random.default_rng(2)
@@ -331,6 +332,54 @@ def test_distributional_agreement_over_episodes(name):
     _record('distribution', m)
     assert abs(m['ticks_per_step_gpu'] / m['ticks_per_step_oracle'] - 1) < (0.10 if name == 'Golf' else 0.05), m
     assert abs(m['done_rate_gpu'] - m['done_rate_oracle']) < 0.05, m
+
+
+@pytest.mark.parametrize('name,n,steps', [('BallBalance', 2048, 26), ('CubesPush', 1024, 500), ('CubesGrasp', 1024, 200)])
+def test_episode_statistics_over_1e4_episodes(name, n, steps):
+    """>= 1e4 finished episodes per side under the same random policy: mean return, mean length and success rate of
+    the CUDA path agree with the oracle's within 4 standard errors (plus 1% of the value for the means)."""
+    from concurrent.futures import ThreadPoolExecutor
+    ob, gb = O.OracleBatch(name, n, seed=41), _batch(name, n, seed=41)
+    rng = np.random.default_rng(11)
+    nthr = min(32, os.cpu_count() or 1)
+    cuts = np.linspace(0, n, nthr + 1).astype(int)
+    gb.reset()
+    ret_o, len_o = np.zeros(n), np.zeros(n, int)
+    ret_g, len_g = np.zeros(n), np.zeros(n, int)
+    eps = {'o': [], 'g': []}
+    with ThreadPoolExecutor(nthr) as ex:
+        list(ex.map(lambda i: ob.reset(lo=int(cuts[i]), hi=int(cuts[i + 1])), range(nthr)))
+        for k in range(steps):
+            a = _actions(rng, name, n); u = rng.uniform(0, 1, n).astype(np.float32).astype(np.float64)
+            gb.step(a, u=u, autoreset=True)                                     # runs while the host threads step the oracle
+            res = list(ex.map(lambda i: ob.step(a, u=u, autoreset=True, lo=int(cuts[i]), hi=int(cuts[i + 1])), range(nthr)))
+            rew = np.zeros(n); done = np.zeros(n, bool); suc = np.zeros(n, bool)
+            for i, r in enumerate(res):
+                sl = slice(int(cuts[i]), int(cuts[i + 1]))
+                rew[sl] = r['reward'][sl]; done[sl] = r['terminated'][sl] | r['truncated'][sl]; suc[sl] = r['success'][sl]
+            ret_o += rew; len_o += 1
+            for i in np.nonzero(done)[0]:
+                eps['o'].append((ret_o[i], len_o[i], suc[i]))
+            ret_o[done] = 0; len_o[done] = 0
+            rew_g, done_g, suc_g = _np(gb.reward), _np((gb.terminated | gb.truncated).bool()), _np(gb.success.bool())
+            ret_g += rew_g; len_g += 1
+            for i in np.nonzero(done_g)[0]:
+                eps['g'].append((ret_g[i], len_g[i], suc_g[i]))
+            ret_g[done_g] = 0; len_g[done_g] = 0
+    eo, eg = np.array(eps['o'], float), np.array(eps['g'], float)
+    m = dict(env=name, episodes_oracle=len(eo), episodes_gpu=len(eg))
+    assert len(eo) >= 10000 and len(eg) >= 10000, m
+    for j, key in enumerate(('return', 'length', 'success')):
+        mo, mg = eo[:, j].mean(), eg[:, j].mean()
+        se = np.sqrt(eo[:, j].var() / len(eo) + eg[:, j].var() / len(eg))
+        m['%s_oracle' % key], m['%s_gpu' % key], m['%s_se' % key] = float(mo), float(mg), float(se)
+    _record('episode_statistics', m)
+    for key in ('return', 'length', 'success'):
+        tol = 4 * m['%s_se' % key] + (0.01 * abs(m['%s_oracle' % key]) if key != 'success' else 0.002)
+        assert abs(m['%s_gpu' % key] - m['%s_oracle' % key]) <= tol, (key, m)
+    st = gb.stats()                                                             # the device-side counters tell the same story
+    assert st['episodes'] == len(eg) and st['successes'] == eg[:, 2].sum()
+    assert st['return_sum'] == pytest.approx(eg[:, 0].sum(), rel=1e-4) and st['length_sum'] == eg[:, 1].sum()
 
 
 # ------------------------------------------------------------------------------------------------- gym-style API
