@@ -28,9 +28,12 @@ WORKLOADS = {  # name -> (env, envs per GPU, BASELINE.json config index)
     'push16384': ('CubesPush', 16384, 3),
     'grasp16384': ('CubesGrasp', 16384, 4),
     'golf16384': ('Golf', 16384, None),
+    'pushdiff16384': ('CubesPushDiff', 16384, None),
+    'golfjoints16384': ('GolfJoints', 16384, None),
 }
 # algorithmic HBM bytes per env-step (SURVEY.md §8d / DESIGN.md §5): state once in, once out, action in, obs/reward/flags out
-BYTES_PER_ENV_STEP = {'BallBalance': 562, 'TwoBallsBalance': 678, 'CubesPush': 606, 'CubesGrasp': 530, 'Golf': 606}
+BYTES_PER_ENV_STEP = {'BallBalance': 562, 'TwoBallsBalance': 678, 'CubesPush': 606, 'CubesGrasp': 530, 'Golf': 606,
+                      'CubesPushDiff': 606, 'GolfJoints': 642}
 METRIC = 'env-steps/sec (batched, device-timed)'
 
 
@@ -40,7 +43,7 @@ def action_sampler(env, n, gen, torch, device):
         a = torch.rand(n, 9, generator=gen, device=device)
         a[:, 2:8] = (a[:, 2:8] * 2 - 1) * 3.14159265
         return a
-    return (torch.rand(n, 3, generator=gen, device=device) * 2 - 1) * 0.1
+    return (torch.rand(n, 6 if env == 'GolfJoints' else 3, generator=gen, device=device) * 2 - 1) * 0.1
 
 
 def peaks():

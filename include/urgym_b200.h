@@ -21,7 +21,10 @@ extern "C" {
 
 typedef struct urgym_env_s* urgym_handle;
 
-enum { URGYM_BALL_BALANCE = 0, URGYM_TWO_BALLS_BALANCE = 1, URGYM_CUBES_PUSH = 2, URGYM_CUBES_GRASP = 3, URGYM_GOLF = 4 };
+/* 5 and 6 are the reference's variants of CubesPush / Golf: same world, other observation / action mapping
+ * (urgym/envs/env_cubes_push_diff_v0.py:209-211; urgym/envs/env_golf_joints_v0.py:60-63,85,123-124,229-234). */
+enum { URGYM_BALL_BALANCE = 0, URGYM_TWO_BALLS_BALANCE = 1, URGYM_CUBES_PUSH = 2, URGYM_CUBES_GRASP = 3, URGYM_GOLF = 4,
+       URGYM_CUBES_PUSH_DIFF = 5, URGYM_GOLF_JOINTS = 6, URGYM_ENV_COUNT = 7 };
 enum { URGYM_OK = 0, URGYM_E_ARG = -1, URGYM_E_CUDA = -2, URGYM_E_STATE = -3 };
 enum { URGYM_STATE_FLOATS = 96, URGYM_MAX_CONTACTS = 16, URGYM_NUM_LINKS = 19, URGYM_NUM_DOF = 12 };
 

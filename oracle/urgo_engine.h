@@ -16,7 +16,11 @@
 
 namespace urgo {
 
-enum { ENV_BALL = 0, ENV_TWO = 1, ENV_PUSH = 2, ENV_GRASP = 3, ENV_GOLF = 4 };
+enum { ENV_BALL = 0, ENV_TWO = 1, ENV_PUSH = 2, ENV_GRASP = 3, ENV_GOLF = 4, ENV_PUSH_DIFF = 5, ENV_GOLF_JOINTS = 6, ENV_COUNT = 7 };
+// The two variants share their parent's world and differ in the action mapping / observation only:
+// env_cubes_push_diff_v0.py:209-211 (cube positions relative to the end effector), env_golf_joints_v0.py:60-63,85,123-124,229-234
+// (six joint displacements instead of an end-effector displacement; the six arm joints prepended to the observation).
+inline int scene_of(int env_type) { return env_type == ENV_PUSH_DIFF ? ENV_PUSH : (env_type == ENV_GOLF_JOINTS ? ENV_GOLF : env_type); }
 enum { NDOF = 12, NMOTOR = 7, MAXFREE = 3, MAXC = 16, STATE_SLOTS = 96 };
 // Movable joints in Bullet link numbering; env code agrees (robot.py:68-73, first six = arm).
 static const int MOV[NDOF] = {1, 2, 3, 4, 5, 6, 9, 11, 13, 14, 16, 18};
@@ -59,7 +63,8 @@ inline V3 box_inertia(double m, V3 h) {
 // Club geometry (env_golf_v0.py:289-332): three 1 kg parts welded; one rigid body about the merged COM.
 static const double CLUB_ZC = (-0.09 + 0.08) / 3.0;  // merged COM z in the club's base frame
 
-inline Scene make_scene(int env_type) {
+inline Scene make_scene(int env_type_full) {
+  const int env_type = scene_of(env_type_full);
   Scene sc; sc.env_type = env_type;
   for (int k = 0; k < 17; k++) {  // robot link boxes (link 0 rests on the table and link 7's 1 cm box is interior)
     const UrgLinkModel& L = URG_LINKS[LINK_ORDER[k]];
@@ -119,6 +124,7 @@ inline Scene make_scene(int env_type) {
       break;
     }
   }
+  if (env_type_full == ENV_GOLF_JOINTS) { sc.obs_dim = 15; sc.act_dim = 6; }
   int ns = (int)sc.shapes.size();
   auto is_free = [&](int i) { return sc.shapes[i].body > 0; };
   auto is_static = [&](int i) { return sc.shapes[i].body < 0; };

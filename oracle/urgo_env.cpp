@@ -55,7 +55,8 @@ struct Env {
     int k = 1; for (double x : v) if (k < 9) trace[at + k++] = x;
   }
 
-  Env(int t, uint64_t s, uint32_t g) : w(t), env_type(t), seed(s), gidx(g) {}
+  int variant;  // the registered env (ENV_PUSH_DIFF / ENV_GOLF_JOINTS differ from their scene in action / observation only)
+  Env(int t, uint64_t s, uint32_t g) : w(t), env_type(scene_of(t)), seed(s), gidx(g), variant(t) {}
 
   static bool settled(double l1_motion) { return l1_motion < BP_SETTLE_THRESHOLD; }
   int settle() {  // wait_until_stable, e.g. env_ball_balance_v0.py:94-103
@@ -177,11 +178,13 @@ struct Env {
         for (int b = 1; b < w.sc.nfree; b++) { V3 d = w.fb[0].pos - w.fb[b].pos; o[3 * b] = d.x; o[3 * b + 1] = d.y; o[3 * b + 2] = d.z; }
         break;
       }
-      case ENV_PUSH:
+      case ENV_PUSH: {
         ee_pose(ep, eq);
         o[0] = ep.x; o[1] = ep.y; o[2] = ep.z;
-        for (int b = 0; b < 2; b++) { o[3 + 3 * b] = w.fb[b].pos.x; o[4 + 3 * b] = w.fb[b].pos.y; o[5 + 3 * b] = w.fb[b].pos.z; }
+        V3 ref = variant == ENV_PUSH_DIFF ? ep : V3();   // env_cubes_push_diff_v0.py:209-211
+        for (int b = 0; b < 2; b++) { V3 d = w.fb[b].pos - ref; o[3 + 3 * b] = d.x; o[4 + 3 * b] = d.y; o[5 + 3 * b] = d.z; }
         break;
+      }
       case ENV_GRASP:
         ee_pose(ep, eq);
         o[0] = approached; o[1] = grasped;
@@ -192,6 +195,7 @@ struct Env {
         break;
       case ENV_GOLF: {
         V3 s = club_foot(), b = w.fb[1].pos, h(0, -0.6, 0.02);
+        if (variant == ENV_GOLF_JOINTS) { for (int i = 0; i < 6; i++) o[i] = w.rob.q[i]; o += 6; }  // env_golf_joints_v0.py:229-234
         o[0] = s.x; o[1] = s.y; o[2] = s.z;
         V3 d1 = s - b, d2 = h - b;
         o[3] = d1.x; o[4] = d1.y; o[5] = d1.z; o[6] = d2.x; o[7] = d2.y; o[8] = d2.z;
@@ -213,6 +217,11 @@ struct Env {
         break;
       }
       case ENV_PUSH: case ENV_GOLF:
+        if (variant == ENV_GOLF_JOINTS) {  // env_golf_joints_v0.py:123-124
+          double t[6]; for (int i = 0; i < 6; i++) t[i] = w.rob.q[i] + a[i];
+          move_ee_joints(t);
+          break;
+        }
         ee_pose(ep, eq);
         move_ee_end(ep + V3(a[0], a[1], a[2]), vertical);
         break;
@@ -342,7 +351,7 @@ using namespace urgo;
 extern "C" {
 
 void* urgo_create(int env_type, int num_envs, uint64_t seed, int env_index_offset) {
-  if (env_type < 0 || env_type > 4 || num_envs <= 0) return nullptr;
+  if (env_type < 0 || env_type >= ENV_COUNT || num_envs <= 0) return nullptr;
   Batch* b = new Batch; b->env_type = env_type;
   b->envs.reserve(num_envs);
   for (int i = 0; i < num_envs; i++) b->envs.emplace_back(env_type, seed, (uint32_t)(env_index_offset + i));

@@ -257,7 +257,10 @@ ENV_CLASSES = {
     'CubesPush': ('urgym.envs.env_cubes_push_v0', 'CubesPush'),
     'CubesGrasp': ('urgym.envs.env_cubes_grasp_v0', 'CubesGrasp'),
     'Golf': ('urgym.envs.env_golf_v0', 'Golf'),
+    'CubesPushDiff': ('urgym.envs.env_cubes_push_diff_v0', 'CubesPush'),
+    'GolfJoints': ('urgym.envs.env_golf_joints_v0', 'Golf'),
 }
+SCENE_OF = {'CubesPushDiff': 'CubesPush', 'GolfJoints': 'Golf'}   # variants live in their parents' worlds
 # the 12 revolute joints in the oracle's DoF order = ascending pybullet joint index
 DOF_JOINTS = [1, 2, 3, 4, 5, 6, 9, 11, 13, 14, 16, 18]
 
@@ -276,6 +279,7 @@ def make_env(name, bullet, **kw):
 
 def body_names(name, env):
     """pybullet body id -> role name used in the fixture."""
+    name = SCENE_OF.get(name, name)
     m = {env.robot.id: 'robot'}
     if name in ('BallBalance', 'TwoBallsBalance', 'CubesPush', 'Golf'):
         m[env.table_id] = 'table'
@@ -317,7 +321,7 @@ def script_free_bodies(bullet, env, name, state, kin):
             p = state[38 + 13 * b: 38 + 13 * b + 13]
             bullet.bodies[ids[key]]['pos'] = tuple(float(v) for v in p[0:3])
             bullet.bodies[ids[key]]['orn'] = tuple(float(v) for v in p[3:7])
-    if name == 'Golf':
+    if SCENE_OF.get(name, name) == 'Golf':
         foot = tuple(kin['club_foot'])
         bullet.link_state[(ids['free0'], 0)] = (foot, (0.0, 0.0, 0.0, 1.0), (0.0,) * 3, (0.0, 0.0, 0.0, 1.0), foot, (0.0, 0.0, 0.0, 1.0))
     return ids
@@ -486,6 +490,8 @@ def main():
 
         # ---- step(): scripted states -> reference outputs
         E['step'] = step_cases(name, env, bullet, O)
+        if name in SCENE_OF:   # the variants share their parents' predicates: a third of the cases covers what differs
+            E['step'] = E['step'][::3]
         G['envs'][name] = E
 
     out = os.path.join(HERE, 'reference_env_logic.json')
@@ -496,6 +502,7 @@ def main():
 
 def contact_menu(name):
     """Contact sets (role, link, role, link) worth exercising for each env's predicates."""
+    name = SCENE_OF.get(name, name)
     R, none = 'robot', []
     if name in ('BallBalance', 'TwoBallsBalance'):
         return [none, [(R, 12, 'free0', -1), (R, 17, 'free0', -1), ('free1', -1, 'free0', -1)]]
@@ -520,10 +527,10 @@ def contact_menu(name):
     raise KeyError(name)
 
 
-def step_cases(name, env, bullet, O):
-    rng = np.random.default_rng(sum(map(ord, name)))
-    t = O.ENV_TYPES[name]
-    ob = O.OracleBatch(name, 1, seed=21)
+def step_cases(full_name, env, bullet, O):
+    name = SCENE_OF.get(full_name, full_name)
+    rng = np.random.default_rng(sum(map(ord, full_name)))
+    ob = O.OracleBatch(full_name, 1, seed=21)
     ob.reset()
     base = ob.get_state()[0].copy()
     ad = ob.ad

@@ -50,7 +50,7 @@ def test_no_torch_or_cxx_types_in_the_signatures():
 
 
 def test_static_queries_work_without_a_device(L):
-    dims = {0: (6, 3, 500), 1: (9, 3, 500), 2: (9, 3, 50), 3: (17, 9, 20), 4: (9, 3, 100)}
+    dims = {0: (6, 3, 500), 1: (9, 3, 500), 2: (9, 3, 50), 3: (17, 9, 20), 4: (9, 3, 100), 5: (9, 3, 50), 6: (15, 6, 100)}
     for t, (od, ad, ms) in dims.items():
         assert (L.urgym_obs_dim(t), L.urgym_act_dim(t), L.urgym_max_episode_steps(t)) == (od, ad, ms)
         g, sm = C.c_int(), C.c_int()

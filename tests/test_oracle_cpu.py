@@ -17,7 +17,8 @@ import oracle_lib as O
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 MODEL = json.load(open(os.path.join(ROOT, 'urgym_b200', 'model', 'ur5_robotiq_85.json')))['links']
 REST = [-1.5690622952052096, -1.5446774605904932, 1.343946009733127, -1.3708613585093699, -1.5707970583733368, 0.0009377758247187636]
-ENVS = ['BallBalance', 'TwoBallsBalance', 'CubesPush', 'CubesGrasp', 'Golf']
+ENVS = ['BallBalance', 'TwoBallsBalance', 'CubesPush', 'CubesGrasp', 'Golf', 'CubesPushDiff', 'GolfJoints']
+SCENE_OF = {'CubesPushDiff': 'CubesPush', 'GolfJoints': 'Golf'}   # variants live in their parents' worlds
 
 
 @pytest.fixture(scope='module', autouse=True)
@@ -175,7 +176,7 @@ def test_reset_is_deterministic_and_layout_independent(name):
     oa, ta = a.reset(); ob, tb = b.reset()
     np.testing.assert_array_equal(oa[2:], ob)          # env i of a shard at offset k == env i+k of the whole batch
     np.testing.assert_array_equal(ta[2:], tb)
-    lo, hi = RESET_TICKS[name]
+    lo, hi = RESET_TICKS[SCENE_OF.get(name, name)]
     assert np.all((ta >= lo) & (ta <= hi)), ta          # 10 arm ticks + the settle loops (regression band)
     if name != 'CubesGrasp':
         assert len({tuple(r) for r in np.round(oa, 9).tolist()}) == 4   # different draws per env
@@ -186,6 +187,7 @@ def test_reset_is_deterministic_and_layout_independent(name):
 @pytest.mark.parametrize('name', ENVS)
 def test_reset_leaves_a_sane_world(name):
     ob = O.OracleBatch(name, 2, seed=4)
+    full_name, name = name, SCENE_OF.get(name, name)
     obs, _ = ob.reset()
     st = ob.get_state()
     facts = O.model_facts()
@@ -207,6 +209,7 @@ def test_reset_leaves_a_sane_world(name):
         np.testing.assert_allclose(zs, 0.02, atol=2.5e-3)                        # 4 cm cubes at rest on the surface
     if name in ('BallBalance', 'TwoBallsBalance'):
         assert np.all(obs[:, 5] < 0)                                             # ball above the paddle
+    assert obs.shape[1] == ob.od and full_name in O.ENV_TYPES
 
 
 def test_free_fall_follows_the_documented_integrator():

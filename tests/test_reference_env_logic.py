@@ -16,7 +16,8 @@ import pytest
 import oracle_lib as O
 
 GOLD = json.load(open(os.path.join(os.path.dirname(__file__), 'golden', 'reference_env_logic.json')))
-ENVS = ['BallBalance', 'TwoBallsBalance', 'CubesPush', 'CubesGrasp', 'Golf']
+ENVS = ['BallBalance', 'TwoBallsBalance', 'CubesPush', 'CubesGrasp', 'Golf', 'CubesPushDiff', 'GolfJoints']
+SCENE_OF = {'CubesPushDiff': 'CubesPush', 'GolfJoints': 'Golf'}   # variants live in their parents' worlds
 EV_IK, EV_GRIPPER, EV_SPAWN, EV_TICKS, EV_SETTLE, EV_JOINTS, EV_RESET_ARM = 1, 2, 3, 4, 5, 6, 7
 
 
@@ -31,7 +32,7 @@ def test_registry_ids_and_episode_limits():
     for env_id, spec in E.SPECS.items():
         assert env_id in reg
         assert reg[env_id]['max_episode_steps'] == spec[1]
-        assert reg[env_id]['entry_point'].endswith(':' + spec[0])
+        assert reg[env_id]['entry_point'].endswith(':' + SCENE_OF.get(spec[0], spec[0]))   # the variants reuse the class names
         assert O.OracleBatch(spec[0], 1).max_steps == spec[1]
     assert sorted(set(reg) - set(E.SPECS)) == sorted(E.UNSUPPORTED)
 
@@ -93,7 +94,7 @@ def test_robot_setup(name):
             gears[e[1][3]] = ch[2]['gearRatio']
     assert gears == dict(zip(m['gear_child_link'], m['gear_ratio']))
     assert {int(k): -v for k, v in r['mimic_children'].items()} == gears
-    assert r['control_method'] == ('joint' if name == 'CubesGrasp' else 'end')
+    assert r['control_method'] == ('joint' if name in ('CubesGrasp', 'GolfJoints') else 'end')
 
 
 @pytest.mark.parametrize('name', ENVS)
@@ -153,6 +154,7 @@ def test_reset_command_sequence(name):
     """reset(): same commands in the same order; spawn positions agree once expressed relative to the kinematic
     quantities (ee position, gripper centre) each side read at that moment."""
     facts = O.model_facts()
+    scene = SCENE_OF.get(name, name)
     for rec in GOLD['envs'][name]['reset']:
         ref = [e for e in rec['events'] if e['op'] in ('reset_arm', 'ticks', 'gripper', 'ik', 'settle') or
                (e['op'] == 'spawn' and e['role'].startswith('free'))]
@@ -177,7 +179,7 @@ def test_reset_command_sequence(name):
                 assert code == EV_SETTLE and 1 <= int(v[0]) <= 480
             elif e['op'] == 'ik':
                 assert code == EV_IK and e['link'] == 7 and e['maxNumIterations'] == facts['ik_iters']
-                if name == 'CubesGrasp':  # target = the pose read back from the robot: compare its meaning, not its value
+                if scene == 'CubesGrasp':  # target = the pose read back from the robot: compare its meaning, not its value
                     np.testing.assert_allclose(e['pos'], ref_kin['ee'][:3], atol=1e-12)
                 else:
                     np.testing.assert_allclose(v[0:3], e['pos'], atol=1e-12)
@@ -188,19 +190,19 @@ def test_reset_command_sequence(name):
                 spawned_ora[e['role']] = v[1:4].copy()
                 np.testing.assert_allclose(v[4:8], e['orn'], atol=1e-12)
         # anchors: what each side's first spawned body is positioned relative to
-        if name in ('BallBalance', 'TwoBallsBalance', 'Golf'):
+        if scene in ('BallBalance', 'TwoBallsBalance', 'Golf'):
             # the oracle's kinematics at spawn time = its state after the first settle; recover them from a twin run
             twin = O.OracleBatch(name, 1, seed=5); twin.set_trace(True)
-            _replay_until_first_spawn(twin, name)
+            _replay_until_first_spawn(twin, scene)
             k = twin.kinematics()
-            if name == 'Golf':
+            if scene == 'Golf':
                 ref_anchor = np.array(ref_kin['gripper_center'])
                 ora_anchor = k['gripper_center'] + [0, 0, facts['club_zc']]  # oracle body origin = merged COM
             else:
                 ref_anchor = np.array([ref_kin['ee'][0], ref_kin['ee'][1], ref_kin['gripper_center'][2]])
                 ora_anchor = np.array([k['ee'][0], k['ee'][1], k['gripper_center'][2]])
             np.testing.assert_allclose(spawned_ora['free0'] - ora_anchor, spawned_ref['free0'] - ref_anchor, atol=1e-12)
-            if name != 'Golf':  # balls are placed relative to the paddle
+            if scene != 'Golf':  # balls are placed relative to the paddle
                 for b in spawned_ref:
                     if b != 'free0':
                         np.testing.assert_allclose(spawned_ora[b] - spawned_ora['free0'], spawned_ref[b] - spawned_ref['free0'], atol=1e-12)
@@ -257,7 +259,7 @@ def test_step_logic(name, idx):
     if 'raises' in c:
         # env_golf_v0.py:146-172 with reward_type='sparse': no branch assigns `success` -> UnboundLocalError in the
         # reference. The oracle (and the CUDA path) define success=False there; nothing to compare.
-        assert name == 'Golf' and c['reward_type'] == 'sparse'
+        assert SCENE_OF.get(name, name) == 'Golf' and c['reward_type'] == 'sparse'
         return
     assert len(tr) == len(c['commands']) == 1
     cmd, code, v = c['commands'][0], int(tr[0][0]), tr[0][1:]

@@ -81,7 +81,9 @@ int launch(urgym_handle h, KParams& P, void* stream) {
     case 1: return launch_env<1>(h, P, st);
     case 2: return launch_env<2>(h, P, st);
     case 3: return launch_env<3>(h, P, st);
-    default: return launch_env<4>(h, P, st);
+    case 4: return launch_env<4>(h, P, st);
+    case 5: return launch_env<5>(h, P, st);
+    default: return launch_env<6>(h, P, st);
   }
 }
 
@@ -113,7 +115,7 @@ int urgym_shape_info(int t, int shape, int* body, int* link) {
 }
 
 int urgym_create(int env_type, int num_envs, int device, uint64_t seed, int env_index_offset, int reward_sparse, urgym_handle* out) {
-  if (!out || num_envs <= 0 || env_type < 0 || env_type > 4) return fail(URGYM_E_ARG, "urgym_create: bad arguments");
+  if (!out || num_envs <= 0 || env_type < 0 || env_type >= UG_ENV_COUNT) return fail(URGYM_E_ARG, "urgym_create: bad arguments");
   int ndev = 0;
   if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev == 0) return fail(URGYM_E_CUDA, "no CUDA device: urgym_b200 has no CPU path");
   if (device < 0 || device >= ndev) return fail(URGYM_E_ARG, "urgym_create: device out of range");
@@ -277,9 +279,9 @@ int urgym_stats(urgym_handle h, double out[6]) {
   return URGYM_OK;
 }
 int urgym_kernel_info(int env_type, int* group_lanes, int* smem_bytes_per_env) {
-  if (env_type < 0 || env_type > 4 || !group_lanes || !smem_bytes_per_env) return fail(URGYM_E_ARG, "urgym_kernel_info: bad arguments");
+  if (env_type < 0 || env_type >= UG_ENV_COUNT || !group_lanes || !smem_bytes_per_env) return fail(URGYM_E_ARG, "urgym_kernel_info: bad arguments");
   *group_lanes = group_size();
-  *smem_bytes_per_env = env_type == 4 ? (int)sizeof(SmemT<EnvRC<4>::value>) : (int)sizeof(SmemT<EnvRC<0>::value>);
+  *smem_bytes_per_env = (env_type == 4 || env_type == 6) ? (int)sizeof(SmemT<EnvRC<4>::value>) : (int)sizeof(SmemT<EnvRC<0>::value>);
   return URGYM_OK;
 }
 // Development aid (only meaningful in a -DUG_PHASE_TIMING build): summed per-phase warp cycles since the last call.

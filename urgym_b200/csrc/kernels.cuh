@@ -3,9 +3,17 @@
 #pragma once
 #include "dev_env.cuh"
 
-template <int ENV, class S>
+// Registered env -> the world it lives in. CubesPushDiff (5) and GolfJoints (6) differ from CubesPush (2) and Golf (4)
+// in the action mapping and the observation only (env_cubes_push_diff_v0.py:209-211,
+// env_golf_joints_v0.py:60-63,85,123-124,229-234).
+template <int ENVF> struct Scene { static constexpr int value = ENVF == 5 ? 2 : (ENVF == 6 ? 4 : ENVF); };
+template <int ENVF> struct ObsDim { static constexpr int value = ENVF == 0 ? 6 : (ENVF == 3 ? 17 : (ENVF == 6 ? 15 : 9)); };
+template <int ENVF> struct ActDim { static constexpr int value = ENVF == 3 ? 9 : (ENVF == 6 ? 6 : 3); };
+
+template <int ENVF, class S>
 UG_DEV void observe(S& s, const DevModel& M, float* o, int lane) {
   // caller guarantees fresh fk_bodies(); every lane computes, lane 0 writes
+  constexpr int ENV = Scene<ENVF>::value;
   f3 ep; m3 eR; ee_pose(s, M, ep, eR);
   float v[17];
   if (ENV == 0 || ENV == 1) {
@@ -17,6 +25,10 @@ UG_DEV void observe(S& s, const DevModel& M, float* o, int lane) {
     v[0] = ep.x; v[1] = ep.y; v[2] = ep.z;
 #pragma unroll
     for (int b = 0; b < 2; b++) { v[3 + 3 * b] = s.fpos[b][0]; v[4 + 3 * b] = s.fpos[b][1]; v[5 + 3 * b] = s.fpos[b][2]; }
+    if (ENVF == 5) {
+#pragma unroll
+      for (int b = 0; b < 2; b++) { v[3 + 3 * b] -= ep.x; v[4 + 3 * b] -= ep.y; v[5 + 3 * b] -= ep.z; }
+    }
   } else if (ENV == 3) {
     q4 eq = link_quat_chain(s.q, M, 7);
     v[0] = (s.flags & FL_APPROACHED) ? 1.f : 0.f; v[1] = (s.flags & FL_GRASPED) ? 1.f : 0.f;
@@ -27,9 +39,15 @@ UG_DEV void observe(S& s, const DevModel& M, float* o, int lane) {
   } else {
     f3 st = club_foot(s), b = ld3(s.fpos[1]), h = mk3(0.f, -0.6f, 0.02f);
     f3 d1 = st - b, d2 = h - b;
-    v[0] = st.x; v[1] = st.y; v[2] = st.z; v[3] = d1.x; v[4] = d1.y; v[5] = d1.z; v[6] = d2.x; v[7] = d2.y; v[8] = d2.z;
+    constexpr int J0 = ENVF == 6 ? 6 : 0;
+    if (ENVF == 6) {
+#pragma unroll
+      for (int i = 0; i < 6; i++) v[i] = s.q[i];
+    }
+    v[J0 + 0] = st.x; v[J0 + 1] = st.y; v[J0 + 2] = st.z; v[J0 + 3] = d1.x; v[J0 + 4] = d1.y; v[J0 + 5] = d1.z;
+    v[J0 + 6] = d2.x; v[J0 + 7] = d2.y; v[J0 + 8] = d2.z;
   }
-  constexpr int OD = ENV == 0 ? 6 : (ENV == 3 ? 17 : 9);
+  constexpr int OD = ObsDim<ENVF>::value;
   if (lane == 0) {
 #pragma unroll
     for (int i = 0; i < OD; i++) o[i] = v[i];
@@ -37,19 +55,20 @@ UG_DEV void observe(S& s, const DevModel& M, float* o, int lane) {
 }
 
 // contact-row capacity per env type: 16 manifold points x 3 rows, plus up to 6 rolling-friction rows in Golf
-template <int ENV> struct EnvRC { static constexpr int value = ENV == 4 ? 54 : 48; };
+template <int ENVF> struct EnvRC { static constexpr int value = Scene<ENVF>::value == 4 ? 54 : 48; };
 
-template <int ENV, int G>
+template <int ENVF, int G>
 __global__ void __launch_bounds__(32) env_kernel(KParams P) {
-  using S = SmemT<EnvRC<ENV>::value>;
-  constexpr int RC = EnvRC<ENV>::value;
+  constexpr int ENV = Scene<ENVF>::value;
+  using S = SmemT<EnvRC<ENVF>::value>;
+  constexpr int RC = EnvRC<ENVF>::value;
   extern __shared__ __align__(16) unsigned char smraw[];
   const Gp<G> gp = make_gp<G>();
   S& s = reinterpret_cast<S*>(smraw)[(threadIdx.x & 31) / G];
   const DevModel& M = *P.model;
   const int env = blockIdx.x * (32 / G) + (threadIdx.x & 31) / G, lane = gp.l;
-  constexpr int OD = ENV == 0 ? 6 : (ENV == 3 ? 17 : 9);
-  constexpr int AD = ENV == 3 ? 9 : 3;
+  constexpr int OD = ObsDim<ENVF>::value;
+  constexpr int AD = ActDim<ENVF>::value;
   if (env >= P.N) return;
   if (P.mode == MODE_RESET && P.mask && !P.mask[env]) return;
   float* rec = P.state + (size_t)env * UG_STATE;
@@ -76,6 +95,12 @@ __global__ void __launch_bounds__(32) env_kernel(KParams P) {
       if (ENV == 1) rew -= fabsf(a[0]) + fabsf(a[1]) + fabsf(a[2]);
       f3 e = euler_from_quat(mat_to_quat(eR));
       move_ee(s, M, ep, quat_from_euler(e.x + a[0], e.y + a[1], e.z + a[2]), gp);
+    } else if (ENVF == 6) {              // env_golf_joints_v0.py:123-124: joint targets = current arm joints + action
+      float t[6];
+#pragma unroll
+      for (int i = 0; i < 6; i++) t[i] = s.q[i] + a[i];
+      gp.sync();
+      set_arm_targets(s, t, lane);
     } else if (ENV == 2 || ENV == 4) {   // env_cubes_push_v0.py:122-126, env_golf_v0.py:122-126
       move_ee(s, M, ep + mk3(a[0], a[1], a[2]), vert, gp);
     } else {                              // env_cubes_grasp_v0.py:121-144
@@ -180,8 +205,8 @@ __global__ void __launch_bounds__(32) env_kernel(KParams P) {
         if (lane < UG_MAXC) { P.contacts[((size_t)env * UG_MAXC + lane) * 2] = lane < nc ? (s.con[lane].shapes & 255) : -1; P.contacts[((size_t)env * UG_MAXC + lane) * 2 + 1] = lane < nc ? (s.con[lane].shapes >> 8) : -1; }
         if (lane == 0) P.ccount[env] = nc;
       }
-      observe<ENV>(s, M, P.obs + (size_t)OD * env, lane);
-      if (P.final_obs) observe<ENV>(s, M, P.final_obs + (size_t)OD * env, lane);
+      observe<ENVF>(s, M, P.obs + (size_t)OD * env, lane);
+      if (P.final_obs) observe<ENVF>(s, M, P.final_obs + (size_t)OD * env, lane);
       if (lane == 0) { P.reward[env] = rew; P.term[env] = term; P.trunc[env] = trunc; P.succ[env] = succ; }
       if ((term || trunc) && lane == 0 && P.stats) {
         atomicAdd(&P.stats[0], 1.0); atomicAdd(&P.stats[1], (double)ep_ret); atomicAdd(&P.stats[2], (double)step_count); atomicAdd(&P.stats[3], succ ? 1.0 : 0.0);
@@ -246,7 +271,7 @@ __global__ void __launch_bounds__(32) env_kernel(KParams P) {
       continue;
     }
     // PH_SETTLE2: reset finished -> first observation of the new episode
-    observe<ENV>(s, M, P.obs + (size_t)OD * env, lane);
+    observe<ENVF>(s, M, P.obs + (size_t)OD * env, lane);
     break;
   }
   if (P.nticks) {

@@ -12,6 +12,7 @@
 #define UG_MAXPAIRS 128
 #define UG_MAXC 16
 #define UG_STATE 96
+#define UG_ENV_COUNT 7  // 0 BallBalance 1 TwoBallsBalance 2 CubesPush 3 CubesGrasp 4 Golf 5 CubesPushDiff 6 GolfJoints
 
 struct DevShape {
   int kind;    // 0 box, 1 sphere
@@ -39,5 +40,5 @@ struct DevModel {
   DevShape shapes[UG_MAXSHAPES]; uint8_t pairs[UG_MAXPAIRS][2];
 };
 
-// Host: fills *m for env_type 0..4. Returns 0 or -1.
+// Host: fills *m for env_type 0..UG_ENV_COUNT-1. Returns 0 or -1.
 int build_model(int env_type, DevModel* m);

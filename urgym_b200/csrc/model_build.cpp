@@ -55,8 +55,10 @@ void box_inertia(double m, const double* h, float* out) {
 
 }  // namespace
 
-int build_model(int env_type, DevModel* m) {
-  if (env_type < 0 || env_type > 4) return -1;
+int build_model(int env_type_full, DevModel* m) {
+  if (env_type_full < 0 || env_type_full >= UG_ENV_COUNT) return -1;
+  // CubesPushDiff (5) and GolfJoints (6) live in their parents' worlds (env_cubes_push_diff_v0.py, env_golf_joints_v0.py)
+  const int env_type = env_type_full == 5 ? 2 : (env_type_full == 6 ? 4 : env_type_full);
   std::memset(m, 0, sizeof(*m));
   int dof_of_link[UG_NLINK];
   for (int i = 0; i < UG_NLINK; i++) dof_of_link[i] = -1;
@@ -135,7 +137,7 @@ int build_model(int env_type, DevModel* m) {
 
   // ---- scene (same shape and pair order as the oracle's make_scene; the order is part of the spec because the
   // contact cap keeps the first UG_MAXC manifold points)
-  m->env_type = env_type; m->gravity = -9.8f;
+  m->env_type = env_type_full; m->gravity = -9.8f;
   int ns = 0;
   for (int k = 0; k < 17; k++) {
     int li = LINK_ORDER[k]; const UrgLinkModel& L = URG_LINKS[li];
@@ -202,6 +204,7 @@ int build_model(int env_type, DevModel* m) {
       break;
     }
   }
+  if (env_type_full == 6) { m->obs_dim = 15; m->act_dim = 6; }   // env_golf_joints_v0.py:60-63
   m->nshapes = ns;
   int np = 0;
   auto add = [&](int a, int b) { if (np < UG_MAXPAIRS) { m->pairs[np][0] = (uint8_t)a; m->pairs[np][1] = (uint8_t)b; } np++; };

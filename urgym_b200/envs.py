@@ -1,4 +1,5 @@
-"""Host-side mirror of the reference's Gymnasium interface for the five in-scope envs.
+"""Host-side mirror of the reference's Gymnasium interface for the in-scope envs (the five of the
+north star plus the two variants CubesPushDiff and GolfJoints).
 
 Reference: /root/reference/urgym/envs/__init__.py:1-50 (ids, max_episode_steps) and the env classes, e.g.
 /root/reference/urgym/envs/env_ball_balance_v0.py:34-173 (`__init__(camera=None, reward_type='dense',
@@ -55,10 +56,13 @@ SPECS = {
     'URGym/CubesGrasp-v0': ('CubesGrasp', 20, ([0] * 2 + [-1.0] * 3 + [-1] * 4 + [0] + [-1.0] * 3 + [-1.0] * 4, [1] * 2 + [1.0] * 3 + [1.0] * 4 + [1] + [1.0] * 3 + [1.0] * 4),
                             ([0] * 2 + [-PI] * 6 + [0], [1] * 2 + [PI] * 6 + [1])),
     'URGym/Golf-v0': ('Golf', 100, ([-1.0] * 9, [1.0] * 9), ([-0.1] * 3, [0.1] * 3)),
+    # variants: same world, other observation / action mapping (env_cubes_push_diff_v0.py:209-211, env_golf_joints_v0.py:60-63)
+    'URGym/CubesPushDiff-v0': ('CubesPushDiff', 50, ([-1.0] * 9, [1.0] * 9), ([-0.1] * 3, [0.1] * 3)),
+    'URGym/GolfJoints-v0': ('GolfJoints', 100, ([-2 * PI] * 6 + [-1.0] * 9, [2 * PI] * 6 + [1.0] * 9), ([-0.1] * 6, [0.1] * 6)),
 }
-# registered by the reference but outside this backend's scope (SURVEY.md §2 rows 7, 8)
-UNSUPPORTED = ('URGym/Box-v0', 'URGym/CubesPushDiff-v0', 'URGym/GolfJoints-v0')
-HAS_SUCCESS_INFO = ('CubesPush', 'CubesGrasp', 'Golf')  # info={'is_success': ...} (env_cubes_push_v0.py:143 etc.)
+# registered by the reference but outside this backend's scope (SURVEY.md §2 row 8, §8f rank 4)
+UNSUPPORTED = ('URGym/Box-v0',)
+HAS_SUCCESS_INFO = ('CubesPush', 'CubesGrasp', 'Golf', 'CubesPushDiff', 'GolfJoints')  # info={'is_success': ...} (env_cubes_push_v0.py:143 etc.)
 
 
 def _spaces(env_id):
@@ -146,7 +150,9 @@ TwoBallsBalance = _mk('URGym/TwoBallsBalance-v0')
 CubesPush = _mk('URGym/CubesPush-v0')
 CubesGrasp = _mk('URGym/CubesGrasp-v0')
 Golf = _mk('URGym/Golf-v0')
-_CLASSES = {c.env_id: c for c in (BallBalance, TwoBallsBalance, CubesPush, CubesGrasp, Golf)}
+CubesPushDiff = _mk('URGym/CubesPushDiff-v0')
+GolfJoints = _mk('URGym/GolfJoints-v0')
+_CLASSES = {c.env_id: c for c in (BallBalance, TwoBallsBalance, CubesPush, CubesGrasp, Golf, CubesPushDiff, GolfJoints)}
 
 
 def make(env_id, **kwargs):
