@@ -54,6 +54,17 @@ def peaks():
     return 6650.0, 'fallback'
 
 
+def ncu_traffic(workload):
+    """(bytes per launch, issue-slot utilisation %) of the dominant kernel from the committed ncu capture, or (None, None)."""
+    p = os.path.join(ROOT, 'profiles', 'ncu_traffic.json')
+    if os.path.exists(p):
+        with open(p) as f:
+            d = json.load(f).get(workload)
+        if d:
+            return d['dram_bytes_read'] + d['dram_bytes_write'], d.get('issue_active_pct')
+    return None, None
+
+
 class ClockSampler:
     Q = 'clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap'
 
@@ -254,13 +265,16 @@ def main():
         peak, how = peaks()
         ms_step = ms_total / K
         achieved = BYTES_PER_ENV_STEP[env] * n_envs / (ms_step * 1e-3) / 1e9
+        traffic, issue_pct = ncu_traffic(args.workload if not args.envs else '')
         line = {'metric': METRIC, 'value': value, 'unit': 'env-steps/s', 'n_gpus': world, 'steps': K, 'warmup': W, 'ms_per_step': ms_step,
                 'higher_is_better': True, 'scaling': 'weak', 'vs_baseline': None, 'dtype': 'f32', 'data': 'synthetic', 'config': config,
                 'ticks_per_env_step': float(gstats[0].item() / max(gstats[1].item(), 1)), 'physics_ticks_per_s': float(gstats[0].item() / (ms_total * 1e-3)),
                 'gpu_launches': int(l1 - l0), 'clocks': clk,
-                'roofline': {'bound': 'hbm', 'achieved': achieved, 'peak': peak, 'unit': 'GB/s', 'frac': achieved / peak, 'traffic': None,
-                             'peak_source': how, 'kernel': 'env_kernel<%s>' % env,
-                             'note': 'latency/issue-bound fused tick loop; see profiles/ for SM issue utilisation'}}
+                'roofline': {'bound': 'hbm', 'achieved': achieved, 'peak': peak, 'unit': 'GB/s', 'frac': achieved / peak,
+                             'traffic': traffic, 'traffic_unit': 'bytes per launch (ncu dram read + write; includes write-back of the L2-flush buffer)',
+                             'algorithmic_bytes_per_launch': BYTES_PER_ENV_STEP[env] * n_envs,
+                             'peak_source': how, 'kernel': 'env_kernel<%s>' % env, 'sm_issue_active_pct': issue_pct,
+                             'note': 'bound by dependent fp32 / shuffle chains of the PGS sweeps, not by HBM; see DESIGN.md section 6 and profiles/'}}
         if e2e:
             line['e2e'] = e2e
         if world == 1 and not args.no_cpu:
