@@ -50,6 +50,8 @@ UG_DEV void rot_sym(const m3& R, const float* s, float* o) {
   o[5] = c0.z * R.m[6] + c1.z * R.m[7] + c2.z * R.m[8];
 }
 
+UG_DEV float rsqrt_ftz(float x) { float r; asm("rsqrt.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x)); return r; }
+
 struct q4 { float x, y, z, w; };
 UG_DEV q4 mkq(float x, float y, float z, float w) { q4 r; r.x = x; r.y = y; r.z = z; r.w = w; return r; }
 UG_DEV q4 qmul(q4 a, q4 b) {

@@ -375,12 +375,16 @@ __device__ __noinline__ float solve_and_integrate(S& s, const DevModel& M, const
     unsigned ci_cur = (unsigned)s.jci4[1];                                                               \
     _Pragma("unroll") for (int sj = 0; sj < NSJ; sj++) {                                                 \
       const int b_ = min(n_nc, sj * G + G);                                                              \
-      _Pragma("unroll 1") for (int row = sj * G; row < b_; row++) UG_JOINT_STEP(row, row + 1, sj, NACT)  \
+      int row = sj * G;                                     /* two rows per trip: half the loop overhead */ \
+      _Pragma("unroll 1") for (; row + 1 < b_; row += 2) { UG_JOINT_STEP(row, row + 1, sj, NACT) UG_JOINT_STEP(row + 1, row + 2, sj, NACT) } \
+      if (row < b_) UG_JOINT_STEP(row, row + 1, sj, NACT)                                                \
     }                                                                                                    \
   } else {                                                                                               \
     unsigned ci_cur = (unsigned)s.jci4[n_nc];                                                            \
     _Pragma("unroll") for (int sj = NSJ - 1; sj >= 0; sj--) {                                            \
-      _Pragma("unroll 1") for (int row = min(n_nc, sj * G + G) - 1; row >= sj * G; row--) UG_JOINT_STEP(row, row - 1, sj, NACT) \
+      int row = min(n_nc, sj * G + G) - 1;                                                               \
+      _Pragma("unroll 1") for (; row - 1 >= sj * G; row -= 2) { UG_JOINT_STEP(row, row - 1, sj, NACT) UG_JOINT_STEP(row - 1, row - 2, sj, NACT) } \
+      if (row >= sj * G) UG_JOINT_STEP(row, row - 1, sj, NACT)                                           \
     }                                                                                                    \
   }
   // normals (contacts 0..NC-1 live in contact slot 0: NC <= 16 <= G), friction limits from this sweep's normal
@@ -421,8 +425,10 @@ __device__ __noinline__ float solve_and_integrate(S& s, const DevModel& M, const
         const float sm = lam[NSJ + so] + d_;                                                             \
         const float ot = __shfl_xor_sync(gp.mask, sm, 1, G); /* the pair's other tangent (pairs start on even rows) */ \
         const float lm = limv[so];                           /* both lanes of a pair carry the same limit */ \
-        float cl = lm;                                                                                   \
-        if (fabsf(sm) > lm || fabsf(ot) > lm) cl = fabsf(lm * sm * rsqrtf(fmaxf(sm * sm + ot * ot, 1e-30f))); \
+        /* implicit cone, branch-free: inside the box |.| <= lm both tangents keep their value, else this one is */ \
+        /* scaled onto the circle of radius lm (rsqrt.approx.ftz: the argument is >= lm^2 > 0 whenever it is used) */ \
+        const float cs = fabsf(lm * sm * rsqrt_ftz(fmaxf(fmaf(sm, sm, ot * ot), 1e-30f)));               \
+        const float cl = fmaxf(fabsf(sm), fabsf(ot)) > lm ? cs : lm;                                     \
         const float sn = fminf(fmaxf(sm, -cl), cl);                                                      \
         d_ = sn - lam[NSJ + so];                                                                         \
         if ((l | 1) == (li | 1)) lam[NSJ + so] = sn;                                                     \
