@@ -7,7 +7,7 @@ import ctypes as C
 import os
 
 HERE = os.path.dirname(os.path.abspath(__file__))
-SO_PATH = os.path.join(HERE, 'liburgym_b200.so')
+SO_PATH = os.environ.get('URGYM_SO') or os.path.join(HERE, 'liburgym_b200.so')   # URGYM_SO: A/B builds of the same ABI
 
 ENV_TYPES = {'BallBalance': 0, 'TwoBallsBalance': 1, 'CubesPush': 2, 'CubesGrasp': 3, 'Golf': 4, 'CubesPushDiff': 5, 'GolfJoints': 6}
 STATE_FLOATS = 96

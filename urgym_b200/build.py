@@ -4,7 +4,7 @@ import subprocess
 import sys
 
 HERE = os.path.dirname(os.path.abspath(__file__))
-SO = os.path.join(HERE, 'liburgym_b200.so')
+SO = os.environ.get('URGYM_SO') or os.path.join(HERE, 'liburgym_b200.so')
 SRC = [os.path.join(HERE, 'csrc', f) for f in ('capi.cu', 'model_build.cpp')]
 
 
