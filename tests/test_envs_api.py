@@ -44,3 +44,6 @@ def test_no_cpu_fallback_for_the_env_classes():
         E.URGymVectorEnv('URGym/Golf-v0', 8)
     with pytest.raises(ValueError):
         E.URGymVectorEnv('URGym/Box-v0', 8)
+    from urgym_b200.sb3_vec_env import URGymSB3VecEnv
+    with pytest.raises(UrgymError):
+        URGymSB3VecEnv('URGym/CubesPush-v0', 8)

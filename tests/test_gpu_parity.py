@@ -412,3 +412,40 @@ def test_vector_env_and_single_env_api():
             break
     assert k == 49 and trunc or term
     e.close()
+
+
+def test_sb3_vec_env_protocol():
+    """SB3 VecEnv conventions (urgym_b200/sb3_vec_env.py): numpy float32 in / out, dones = terminated | truncated with the
+    next episode's first observation returned, terminal_observation / TimeLimit.truncated / is_success in infos."""
+    from urgym_b200.sb3_vec_env import URGymSB3VecEnv
+    v = URGymSB3VecEnv('URGym/CubesGrasp-v0', 64, seed=3)
+    obs = v.reset()
+    assert obs.shape == (64, 17) and obs.dtype == np.float32
+    ref = _batch('CubesGrasp', 64, seed=3); ref.reset()
+    rng = np.random.default_rng(12)
+    for k in range(21):
+        a = _actions(rng, 'CubesGrasp', 64).astype(np.float32)
+        obs, rew, dones, infos = v.step(a)
+        ref.step(a, autoreset=True)
+        np.testing.assert_array_equal(obs, _np(ref.obs))                       # same kernel, same seeds: bit-exact
+        np.testing.assert_array_equal(rew, _np(ref.reward))
+        assert dones.dtype == bool and len(infos) == 64 and all('is_success' in i for i in infos)
+        if k == 19:
+            assert dones.all()
+            assert all(i['TimeLimit.truncated'] and i['terminal_observation'].shape == (17,) for i in infos)
+            np.testing.assert_array_equal(np.stack([i['terminal_observation'] for i in infos]), _np(ref.final_obs))
+        elif k < 19:
+            assert not any('terminal_observation' in i for i, d in zip(infos, dones) if not d)
+    assert v.env_is_wrapped(object) == [False] * 64 and v.get_attr('num_envs', [0, 1]) == [64, 64]
+    v.close()
+
+
+def test_trace_recorded_on_the_device_replays_on_the_oracle(tmp_path):
+    from urgym_b200 import trace as T
+    gb = _batch('CubesPush', 16, seed=6); gb.reset()
+    rng = np.random.default_rng(13)
+    tr = T.record(gb, 'CubesPush', rng.uniform(-0.1, 0.1, (6, 16, 3)).astype(np.float32))
+    T.save(str(tmp_path / 't.npz'), tr)
+    ob = O.OracleBatch('CubesPush', 16, seed=1); ob.reset()
+    d = T.replay(ob, T.load(str(tmp_path / 't.npz')), resync=True)
+    assert d['same_ticks'].mean() >= 0.9 and d['same_flags'].min() == 1.0 and np.median(d['obs_err']) < 1e-4, d
