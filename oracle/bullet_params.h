@@ -36,6 +36,10 @@
 #define BP_IK_DAMPING 0.5                 // default per-joint damping added to the diagonal of J^T J
 #define BP_IK_RESIDUAL 1e-4               // default residualThreshold (position error)
 #define BP_IK_MAX_STEP 0.7853981633974483 // BussIK MaxAngleDLS = 45 degrees
+// --- capacity choice of this implementation (not Bullet's): rolling-friction rows are built for the first 3 manifolds
+//     that carry rolling friction in a tick (Golf: ball on pitch + two club parts); a ball touching four things at once
+//     keeps normal and sliding friction on all of them
+#define BP_MAX_ROLLING_CONTACTS 3
 // --- settle loop given by the reference: env_ball_balance_v0.py:94-103
 #define BP_SETTLE_MAX_TICKS 480
 #define BP_SETTLE_THRESHOLD 5e-3

@@ -465,7 +465,7 @@ struct World {
       n.rhs = (pos_e + vel_e) * n.invd; n.lo = 0; n.hi = 1e10;
       int nidx = (int)nr.size(); nr.push_back(n);
       V3 t1, t2; plane_space(c.n, t1, t2);
-      if (c.roll > 0) {
+      if (c.roll > 0 && (int)tr.size() < 2 * BP_MAX_ROLLING_CONTACTS) {
         for (int k = 0; k < 2; k++) {
           Row t; V3 dir = k == 0 ? t1 : t2;
           add_side(t, A, c.posA, dir, false, 1.0); add_side(t, B, c.posB, dir, false, -1.0); finish_row(t);

@@ -30,44 +30,72 @@ UG_DEV void shape_box(const S& s, const DevShape& Sh, BoxW& b) {
   b.h = ld3(Sh.half);
 }
 
-// Lane per candidate pair; manifold points are appended in pair order and capped at UG_MAXC.
+template <class S>
+UG_DEV f3 shape_center(const S& s, const DevShape& Sh) {
+  const f3 lc = ld3(Sh.lc);
+  if (Sh.body == 0) return ld3(s.bp[Sh.rbody]) + mulv(ldm(s.bR[Sh.rbody]), lc);
+  if (Sh.body > 0) return ld3(s.fpos[Sh.body - 1]) + mulv(ldm(s.fR[Sh.body - 1]), lc);
+  return lc;
+}
+
+// Two passes. Pass 1, lane per candidate pair: bounding-sphere cull (sphere against the static boxes themselves),
+// survivors are compacted in pair order into a byte list in the (idle) solver scratch. Pass 2, lane per surviving pair:
+// narrowphase. Manifold points are appended in pair order and capped at UG_MAXC; the order is the
+// oracle's because the compaction keeps it. A tick with 113 candidate pairs (Golf) and 9 close ones costs one
+// narrowphase round instead of four.
 template <int G, class S>
 __device__ __noinline__ void collide(S& s, const DevModel& M, const Gp<G> gp) {
   const int l = gp.l;
-  int base = 0;
+  unsigned char* near_list = reinterpret_cast<unsigned char*>(s.u.T);  // UG_MAXPAIRS bytes; T is dead between ticks
+  int nnear = 0;
 #pragma unroll 1
-  for (int p0 = 0; p0 < M.npairs && base < UG_MAXC; p0 += G) {
-    int p = p0 + l, n = 0, sa = 0, sb = 0;
-    CPt pts[4];
+  for (int p0 = 0; p0 < M.npairs; p0 += G) {
+    const int p = p0 + l;
+    bool near = false;
     if (p < M.npairs) {
-      sa = M.pairs[p][0]; sb = M.pairs[p][1];
-      const DevShape& A = M.shapes[sa]; const DevShape& B = M.shapes[sb];
-      bool actA = A.body <= 0 || (s.flags & (FL_BODY0 << (A.body - 1)));
-      bool actB = B.body <= 0 || (s.flags & (FL_BODY0 << (B.body - 1)));
+      const DevShape& A = M.shapes[M.pairs[p][0]]; const DevShape& B = M.shapes[M.pairs[p][1]];
+      const bool actA = A.body <= 0 || (s.flags & (FL_BODY0 << (A.body - 1)));
+      const bool actB = B.body <= 0 || (s.flags & (FL_BODY0 << (B.body - 1)));
       if (actA && actB) {
-        float margin = fminf(A.cbt, B.cbt);
-        BoxW a, b; shape_box(s, A, a); shape_box(s, B, b);
-        f3 dc = a.c - b.c;
-        bool near;
-        if (B.body < 0) {
-          f3 e = mk3(fmaxf(fabsf(dc.x) - b.h.x, 0.f), fmaxf(fabsf(dc.y) - b.h.y, 0.f), fmaxf(fabsf(dc.z) - b.h.z, 0.f));
+        const float margin = fminf(A.cbt, B.cbt);
+        const f3 ca = shape_center(s, A), cb = shape_center(s, B);
+        const f3 dc = ca - cb;
+        if (B.body < 0) {  // static boxes are axis-aligned in the world (table, plane, pitch)
+          const f3 h = ld3(B.half);
+          const f3 e = mk3(fmaxf(fabsf(dc.x) - h.x, 0.f), fmaxf(fabsf(dc.y) - h.y, 0.f), fmaxf(fabsf(dc.z) - h.z, 0.f));
           near = norm3(e) <= A.brad + margin;
         } else near = norm3(dc) <= A.brad + B.brad + margin;
-        if (near) {
-          if (A.kind == 0 && B.kind == 0) n = box_box(a, b, margin, pts);
-          else if (A.kind == 1 && B.kind == 0) {
-            f3 ob, nb; float d;
-            if (sphere_box(a.c, A.radius, b, margin, ob, nb, d)) { pts[0].n = nb; pts[0].dist = d; pts[0].posB = ob; pts[0].posA = ob + nb * d; n = 1; }
-          } else if (A.kind == 0 && B.kind == 1) {
-            f3 oa, na; float d;
-            if (sphere_box(b.c, B.radius, a, margin, oa, na, d)) { pts[0].n = -na; pts[0].dist = d; pts[0].posA = oa; pts[0].posB = oa + na * d; n = 1; }
-          } else {
-            float len = norm3(dc), d = len - A.radius - B.radius;
-            if (d < margin) {
-              f3 nn = len > 1e-12f ? dc * (1.0f / len) : mk3(1, 0, 0);
-              pts[0].n = nn; pts[0].dist = d; pts[0].posB = b.c + nn * B.radius; pts[0].posA = pts[0].posB + nn * d; n = 1;
-            }
-          }
+      }
+    }
+    const unsigned m = gp.ballot(near);
+    if (near) near_list[nnear + __popc(m & ((1u << l) - 1u))] = (unsigned char)p;
+    nnear += __popc(m);
+  }
+  gp.sync();
+  int base = 0;
+#pragma unroll 1
+  for (int i0 = 0; i0 < nnear && base < UG_MAXC; i0 += G) {
+    int n = 0, sa = 0, sb = 0;
+    CPt pts[4];
+    if (i0 + l < nnear) {
+      const int p = near_list[i0 + l];
+      sa = M.pairs[p][0]; sb = M.pairs[p][1];
+      const DevShape& A = M.shapes[sa]; const DevShape& B = M.shapes[sb];
+      const float margin = fminf(A.cbt, B.cbt);
+      BoxW a, b; shape_box(s, A, a); shape_box(s, B, b);
+      const f3 dc = a.c - b.c;
+      if (A.kind == 0 && B.kind == 0) n = box_box(a, b, margin, pts);
+      else if (A.kind == 1 && B.kind == 0) {
+        f3 ob, nb; float d;
+        if (sphere_box(a.c, A.radius, b, margin, ob, nb, d)) { pts[0].n = nb; pts[0].dist = d; pts[0].posB = ob; pts[0].posA = ob + nb * d; n = 1; }
+      } else if (A.kind == 0 && B.kind == 1) {
+        f3 oa, na; float d;
+        if (sphere_box(b.c, B.radius, a, margin, oa, na, d)) { pts[0].n = -na; pts[0].dist = d; pts[0].posA = oa; pts[0].posB = oa + na * d; n = 1; }
+      } else {
+        float len = norm3(dc), d = len - A.radius - B.radius;
+        if (d < margin) {
+          f3 nn = len > 1e-12f ? dc * (1.0f / len) : mk3(1, 0, 0);
+          pts[0].n = nn; pts[0].dist = d; pts[0].posB = b.c + nn * B.radius; pts[0].posA = pts[0].posB + nn * d; n = 1;
         }
       }
     }
@@ -168,13 +196,16 @@ __device__ __noinline__ float solve_and_integrate(S& s, const DevModel& M, const
     if (l < NC) s.cdesc[l] = l | (RT_NORMAL << 8);
     bool rl = l < NC && s.con[l].roll > 0.f;
     unsigned rm = gp.ballot(rl);
-    NT = 2 * __popc(rm);
-    if (rl) { int r = __popc(rm & ((1u << l) - 1u)); s.cdesc[NC + 2 * r] = l | (RT_ROLL << 8); s.cdesc[NC + 2 * r + 1] = l | (RT_ROLL << 8) | (1 << 12); }
+    NT = 2 * min(__popc(rm), UGP_MAX_ROLLING_CONTACTS);  // row capacity: RC = 16 + 32 + 2 * UGP_MAX_ROLLING_CONTACTS
+    if (rl) {
+      int r = __popc(rm & ((1u << l) - 1u));
+      if (r < UGP_MAX_ROLLING_CONTACTS) { s.cdesc[NC + 2 * r] = l | (RT_ROLL << 8); s.cdesc[NC + 2 * r + 1] = l | (RT_ROLL << 8) | (1 << 12); }
+    }
     fr0 = NC + NT;
     if (fr0 & 1) { if (l == 0) s.cdesc[fr0] = RT_PAD << 8; fr0++; }
     if (l < NC) { s.cdesc[fr0 + 2 * l] = l | (RT_FRIC << 8); s.cdesc[fr0 + 2 * l + 1] = l | (RT_FRIC << 8) | (1 << 12); }
     Rc = NC > 0 ? fr0 + 2 * NC : 0;
-    if (Rc > RC) Rc = RC;  // cannot happen for the five envs (RC covers 16 contacts + their rolling rows)
+    // Rc <= 16 + 6 + 32 = 54 = RC of the Golf scenes; the other scenes have no rolling friction (Rc <= 48)
   }
   gp.sync();
   // ---- per-lane row registers: slots [0, NSJ) joint rows, [NSJ, NS) contact rows

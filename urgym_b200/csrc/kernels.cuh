@@ -58,7 +58,7 @@ UG_DEV void observe(S& s, const DevModel& M, float* o, int lane) {
 template <int ENVF> struct EnvRC { static constexpr int value = Scene<ENVF>::value == 4 ? 54 : 48; };
 
 template <int ENVF, int G>
-__global__ void __launch_bounds__(32) env_kernel(KParams P) {
+__global__ void __launch_bounds__(32, 13) env_kernel(KParams P) {
   constexpr int ENV = Scene<ENVF>::value;
   using S = SmemT<EnvRC<ENVF>::value>;
   constexpr int RC = EnvRC<ENVF>::value;

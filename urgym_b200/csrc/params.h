@@ -27,6 +27,8 @@
 #define UGP_IK_DAMPING 0.5f
 #define UGP_IK_RESIDUAL 1e-4f
 #define UGP_IK_MAX_STEP 0.7853981633974483f
+// capacity choice shared with the oracle (bullet_params.h): rolling-friction rows for the first 3 rolling manifolds of a tick
+#define UGP_MAX_ROLLING_CONTACTS 3
 #define UGP_SETTLE_MAX_TICKS 480
 #define UGP_SETTLE_THRESHOLD 5e-3f
 #define UGP_RESET_ARM_TICKS 10
