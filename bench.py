@@ -272,7 +272,8 @@ def main():
                 'gpu_launches': int(l1 - l0), 'clocks': clk,
                 'roofline': {'bound': 'hbm', 'achieved': achieved, 'peak': peak, 'unit': 'GB/s', 'frac': achieved / peak,
                              'traffic': traffic, 'traffic_unit': 'bytes per launch (ncu dram read + write; includes write-back of the L2-flush buffer)',
-                             'algorithmic_bytes_per_launch': BYTES_PER_ENV_STEP[env] * n_envs,
+                             'algorithmic_bytes_per_launch': BYTES_PER_ENV_STEP[env] * n_envs, 'launches_per_step': (l1 - l0) / K,
+                             'launch_note': 'one gym step = the env_kernel step grid, plus (ball scenes) the same kernel once more as a reset-only grid over the finished envs; achieved = bytes of the whole step / device time of the whole step',
                              'peak_source': how, 'kernel': 'env_kernel<%s>' % env, 'sm_issue_active_pct': issue_pct,
                              'note': 'bound by dependent fp32 / shuffle chains of the PGS sweeps, not by HBM; see DESIGN.md section 6 and profiles/'}}
         if e2e:

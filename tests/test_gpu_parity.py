@@ -311,6 +311,28 @@ def test_determinism_across_runs():
     np.testing.assert_array_equal(outs[0][0], outs[1][0]); np.testing.assert_array_equal(outs[0][1], outs[1][1])
 
 
+@pytest.mark.parametrize('name', ['BallBalance', 'Golf'])
+def test_reset_launch_scheduling_leaves_results_unchanged(name, monkeypatch):
+    """Auto-resets run inside the step launch or in a reset-only launch that follows it; which one is a
+    scheduling choice per env type and must not change a single bit of what the caller sees."""
+    outs = []
+    for split in ('0', '1'):
+        monkeypatch.setenv('URGYM_SPLIT_RESET', split)
+        gb = _batch(name, 3000, seed=23)
+        gb.reset()
+        rng = np.random.default_rng(12)
+        rec = []
+        for _ in range(6):
+            gb.step(_actions(rng, name, 3000), autoreset=True)
+            rec.append([_np(x).copy() for x in (gb.obs, gb.reward, gb.terminated, gb.truncated, gb.success, gb.final_obs, gb.nticks)])
+        rec.append([_np(gb.get_state()).copy()])
+        outs.append(rec)
+        assert gb.stats()['episodes'] > 0
+    for a, b in zip(outs[0], outs[1]):
+        for x, y in zip(a, b):
+            np.testing.assert_array_equal(x, y)
+
+
 @pytest.mark.parametrize('name', ['BallBalance', 'CubesGrasp', 'Golf'])
 def test_distributional_agreement_over_episodes(name):
     """Free-running (no re-synchronisation) rollouts diverge trajectory by trajectory — the dynamics are chaotic — but

@@ -37,16 +37,27 @@ struct urgym_env_s {
   // staging for the *_host entry points
   float *d_action = nullptr, *d_u = nullptr, *d_draws = nullptr, *d_obs = nullptr, *d_final = nullptr, *d_reward = nullptr;
   uint8_t *d_term = nullptr, *d_trunc = nullptr, *d_succ = nullptr, *d_mask = nullptr; int32_t* d_nticks = nullptr;
+  uint8_t* d_defer = nullptr; bool split_reset = false;  // auto-reset in its own launch
   cudaStream_t own_stream = nullptr, last_stream = nullptr;
 };
 
 namespace {
 
-// G lanes of a warp run one env. URGYM_GROUP=32 selects the warp-per-env variant (for comparison runs).
+// G lanes of a warp run one env: a whole warp by default, URGYM_GROUP=16 packs two envs into a warp
+// (kept for comparison runs).
 int group_size() {
   static int g = 0;
   if (!g) { const char* e = getenv("URGYM_GROUP"); g = (e && atoi(e) == 32) ? 32 : (e && atoi(e) == 16 ? 16 : UG_DEFAULT_GROUP); }
   return g;
+}
+
+// Whether auto-resets run in a launch of their own. Measured per env type (profiles/r01_reset_scheduling.txt): the
+// ball scenes gain 7-19% because step ticks and the robot-only ticks of a reset no longer share an SM, the scenes whose
+// reset settles for hundreds of ticks (Golf) lose to the latency of a thin second grid. URGYM_SPLIT_RESET=0/1 overrides.
+bool default_split_reset(int env_type) {
+  static const bool dflt[UG_ENV_COUNT] = {true, true, false, false, false, false, false};
+  const char* e = getenv("URGYM_SPLIT_RESET");
+  return e ? atoi(e) != 0 : dflt[env_type];
 }
 
 template <int ENV, int G>
@@ -123,6 +134,7 @@ int urgym_create(int env_type, int num_envs, int device, uint64_t seed, int env_
   if (getenv("URGYM_STACK")) CK(cudaDeviceSetLimit(cudaLimitStackSize, (size_t)atoi(getenv("URGYM_STACK"))));
   urgym_handle h = new urgym_env_s;
   h->env_type = env_type; h->N = num_envs; h->device = device; h->seed = seed; h->gidx0 = env_index_offset; h->sparse = reward_sparse;
+  h->split_reset = default_split_reset(env_type);
   if (build_model(env_type, &h->hmodel)) { delete h; return fail(URGYM_E_ARG, "model build failed"); }
   size_t n = (size_t)num_envs; int od = h->hmodel.obs_dim, ad = h->hmodel.act_dim;
   CK(cudaMalloc(&h->dmodel, sizeof(DevModel)));
@@ -138,6 +150,7 @@ int urgym_create(int env_type, int num_envs, int device, uint64_t seed, int env_
   CK(cudaMalloc(&h->d_obs, n * od * sizeof(float))); CK(cudaMalloc(&h->d_final, n * od * sizeof(float))); CK(cudaMalloc(&h->d_reward, n * sizeof(float)));
   CK(cudaMalloc(&h->d_term, n)); CK(cudaMalloc(&h->d_trunc, n)); CK(cudaMalloc(&h->d_succ, n)); CK(cudaMalloc(&h->d_mask, n));
   CK(cudaMalloc(&h->d_nticks, n * 2 * sizeof(int32_t)));
+  CK(cudaMalloc(&h->d_defer, n)); CK(cudaMemset(h->d_defer, 0, n));
   CK(cudaStreamCreateWithFlags(&h->own_stream, cudaStreamNonBlocking));
   std::vector<float> init(n * UG_STATE, 0.f);
   for (size_t i = 0; i < n; i++) { float* r = init.data() + i * UG_STATE; r[37] = 1.f; for (int b = 0; b < UG_MAXFREE; b++) r[38 + 13 * b + 6] = 1.f; }
@@ -150,7 +163,7 @@ int urgym_destroy(urgym_handle h) {
   if (!h) return URGYM_OK;
   cudaSetDevice(h->device);
   cudaDeviceSynchronize();
-  void* ptrs[] = {h->dmodel, h->state, h->contacts, h->ccount, h->stats, h->d_action, h->d_u, h->d_draws, h->d_obs, h->d_final, h->d_reward, h->d_term, h->d_trunc, h->d_succ, h->d_mask, h->d_nticks};
+  void* ptrs[] = {h->dmodel, h->state, h->contacts, h->ccount, h->stats, h->d_action, h->d_u, h->d_draws, h->d_obs, h->d_final, h->d_reward, h->d_term, h->d_trunc, h->d_succ, h->d_mask, h->d_nticks, h->d_defer};
   for (void* p : ptrs) if (p) cudaFree(p);
   if (h->own_stream) cudaStreamDestroy(h->own_stream);
   delete h;
@@ -171,7 +184,14 @@ int urgym_step(urgym_handle h, const float* action_dev, const float* u_dev, cons
   KParams P; std::memset(&P, 0, sizeof(P));
   P.mode = MODE_STEP; P.action = action_dev; P.u = u_dev; P.draws = draws_dev; P.obs = obs_dev; P.reward = reward_dev;
   P.term = terminated_dev; P.trunc = truncated_dev; P.succ = success_dev; P.final_obs = final_obs_dev; P.nticks = nticks_dev; P.autoreset = autoreset;
-  return launch(h, P, stream);
+  if (!autoreset || !h->split_reset) return launch(h, P, stream);
+  // Two launches, same arithmetic per env: the step grid flags the finished envs, a reset-only grid follows (§4.5).
+  P.defer = h->d_defer;
+  int rc = launch(h, P, stream);
+  if (rc) return rc;
+  KParams R; std::memset(&R, 0, sizeof(R));
+  R.mode = MODE_RESET; R.mask = h->d_defer; R.draws = draws_dev; R.obs = obs_dev; R.nticks = nticks_dev; R.deferred_pass = 1;
+  return launch(h, R, stream);
 }
 
 int urgym_step_logic(urgym_handle h, const float* action_dev, const float* u_dev, const int32_t* pairs_dev, const int32_t* count_dev,

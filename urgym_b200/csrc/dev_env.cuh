@@ -11,6 +11,9 @@ struct KParams {
   int32_t* contacts; int32_t* ccount; double* stats;
   const int32_t* inject_pairs; const int32_t* inject_count;  // urgym_step_logic only: contact set instead of physics
   unsigned long long seed; int gidx0; int autoreset; int mode; int raw_ticks; int sparse;
+  // auto-reset in a launch of its own: the step launch flags finished envs in `defer` instead of
+  // resetting them; a MODE_RESET launch over that mask (deferred_pass = 1) follows on the same stream
+  uint8_t* defer; int deferred_pass;
 };
 enum { MODE_STEP = 0, MODE_RESET = 1, MODE_TICKS = 2 };
 enum { PH_STEP = 0, PH_ARM10 = 1, PH_SETTLE1 = 2, PH_SETTLE2 = 3, PH_RAW = 4 };

@@ -211,6 +211,10 @@ __global__ void __launch_bounds__(32, 13) env_kernel(KParams P) {
       if ((term || trunc) && lane == 0 && P.stats) {
         atomicAdd(&P.stats[0], 1.0); atomicAdd(&P.stats[1], (double)ep_ret); atomicAdd(&P.stats[2], (double)step_count); atomicAdd(&P.stats[3], succ ? 1.0 : 0.0);
       }
+      if (P.defer) {  // the reset runs in the launch that follows
+        if (lane == 0) P.defer[env] = (uint8_t)(term || trunc);
+        break;
+      }
       if ((term || trunc) && P.autoreset) { begin_reset(); continue; }
       break;
     }
@@ -276,7 +280,7 @@ __global__ void __launch_bounds__(32, 13) env_kernel(KParams P) {
   }
   if (P.nticks) {
     if (P.mode == MODE_STEP) { if (lane == 0) { P.nticks[2 * env] = ticks_step; P.nticks[2 * env + 1] = ticks_reset; } }
-    else if (lane == 0) P.nticks[env] = P.mode == MODE_RESET ? ticks_reset : n;
+    else if (lane == 0) P.nticks[P.deferred_pass ? 2 * env + 1 : env] = P.mode == MODE_RESET ? ticks_reset : n;
   }
   if (lane == 0 && P.stats) { if (P.mode == MODE_STEP) atomicAdd(&P.stats[4], 1.0); atomicAdd(&P.stats[5], (double)tick_total); }
   store_state(s, rec, gp, step_count, episode, vert, ep_ret);
