@@ -105,6 +105,7 @@ struct Gp {
   __device__ __forceinline__ float shfl(float v, int src) const { return __shfl_sync(mask, v, src, G); }
   __device__ __forceinline__ int shfl(int v, int src) const { return __shfl_sync(mask, v, src, G); }
   __device__ __forceinline__ unsigned ballot(bool p) const { return (__ballot_sync(mask, p) >> shift) & (G == 32 ? 0xffffffffu : ((1u << (G & 31)) - 1u)); }
+  __device__ __forceinline__ bool any(bool p) const { return ballot(p) != 0u; }
   __device__ __forceinline__ float sum(float v) const {
 #pragma unroll
     for (int o = G / 2; o > 0; o >>= 1) v += __shfl_xor_sync(mask, v, o, G);

@@ -166,6 +166,45 @@ UG_DEV void build_crow(const S& s, const DevModel& M, int desc, CRow& r, bool ro
 
 UG_DEV f3 pick3(const f3* a, int b) { return b == 0 ? a[0] : (b == 1 ? a[1] : a[2]); }
 
+// All PGS sweeps of a contact-free tick with exactly N joint rows, warp per env: lane l owns row l and keeps the
+// couplings of its row to every row of the sweep in registers, so a Gauss-Seidel step is FFMA, 2 x FMNMX, SHFL, FFMA
+// plus the owner's impulse update: no operand loads, no address arithmetic, no loop counter, no guards. The operations
+// and their order are those of the generic sweep (same bits). Returns the number of sweeps done; lam0 = the impulse.
+template <int N, class S>
+UG_DEV int joint_sweeps_reg(const S& s, const Gp<32>& gp, unsigned aE_own, float rhs0, float invd0, float lo0, float hi0, float den0, float& lam0) {
+  const int l = gp.l;
+  float e[N];
+#pragma unroll
+  for (int r = 0; r < N; r++) e[r] = lds(aE_own + (unsigned)s.jci4[r + 1]);
+  float w0 = 0.f;
+  int it = 0;
+#define UG_JR_STEP(R)                                                                                    \
+  {                                                                                                      \
+    float d_ = fmaf(-w0, invd0, rhs0);                                                                   \
+    d_ = fminf(fmaxf(d_, blo), bhi);                                                                     \
+    const float delta = gp.shfl(d_, (R));                                                                \
+    if (l == (R)) lam0 += delta;                                                                         \
+    w0 = fmaf(e[(R)], delta, w0);                                                                        \
+  }
+#pragma unroll 1
+  for (; it < UGP_SOLVER_ITERS;) {
+    // a lane's impulse changes only at its own step, so its clamp bounds are constant over the sweep
+    const float blo = lo0 - lam0, bhi = hi0 - lam0, lamp0 = lam0;
+    if (it & 1) {
+#pragma unroll
+      for (int r = 0; r < N; r++) UG_JR_STEP(r)
+    } else {
+#pragma unroll
+      for (int r = N - 1; r >= 0; r--) UG_JR_STEP(r)
+    }
+    it++;
+    const float r_ = (lam0 - lamp0) * den0;
+    if (!gp.any(r_ * r_ > UGP_RESIDUAL_THRESHOLD)) break;
+  }
+#undef UG_JR_STEP
+  return it;
+}
+
 // Returns dt * sum |qd| over the 12 joints after the tick (the quantity wait_until_stable thresholds).
 // The sweep loops are kept rolled and small on purpose: one Gauss-Seidel sweep has to stay resident in the ~6 KB L0
 // instruction cache, because it runs 50 times per tick and is ~80 % of the kernel's time (profiles/).
@@ -384,7 +423,7 @@ __device__ __noinline__ float solve_and_integrate(S& s, const DevModel& M, const
     ci_cur = (unsigned)s.jci4[(NEXT) + 1];                                                               \
     const int li_ = (ROW) - (SJ) * G;                                                                    \
     float d_ = fmaf(-w[SJ], invd[SJ], rhs[SJ]);                                                          \
-    d_ = fminf(fmaxf(d_, lo[SJ] - lam[SJ]), hi[SJ] - lam[SJ]);                                           \
+    d_ = fminf(fmaxf(d_, jlo[SJ]), jhi[SJ]);                                                             \
     const float delta = gp.shfl(d_, li_);                                                                \
     if (l == li_) lam[SJ] += delta;                                                                      \
     _Pragma("unroll") for (int k_ = 0; k_ < NSJ; k_++) w[k_] = fmaf(ej_[k_], delta, w[k_]);              \
@@ -402,6 +441,9 @@ __device__ __noinline__ float solve_and_integrate(S& s, const DevModel& M, const
     _Pragma("unroll") for (int o_ = 0; o_ < (NACT); o_++) { w[NSJ + o_] = fmaf(uc_[o_], DA, w[NSJ + o_]); if (PAIR) w[NSJ + o_] = fmaf(vc_[o_], DB, w[NSJ + o_]); }
   // joint rows, order alternates with the iteration parity (backward on even sweeps)
 #define UG_JOINT_SWEEP(NACT)                                                                             \
+  /* a lane's impulse changes only at its own step, so its clamp bounds are constant over the sweep */  \
+  float jlo[NSJ], jhi[NSJ];                                                                              \
+  _Pragma("unroll") for (int k_ = 0; k_ < NSJ; k_++) { jlo[k_] = lo[k_] - lam[k_]; jhi[k_] = hi[k_] - lam[k_]; } \
   if (it & 1) {                                                                                          \
     unsigned ci_cur = (unsigned)s.jci4[1];                                                               \
     _Pragma("unroll") for (int sj = 0; sj < NSJ; sj++) {                                                 \
@@ -423,10 +465,11 @@ __device__ __noinline__ float solve_and_integrate(S& s, const DevModel& M, const
   // implicit cone
 #define UG_CONTACT_SWEEP(NACT)                                                                           \
   {                                                                                                      \
+    const float nlo = lo[NSJ] - lam[NSJ], nhi = hi[NSJ] - lam[NSJ];   /* constant over the sweep, as above */ \
     _Pragma("unroll 1") for (int row = 0; row < NC; row++) {                                             \
       UG_CONTACT_LOAD(row, false, NACT)                                                                  \
       float d_ = fmaf(-w[NSJ], invd[NSJ], rhs[NSJ]);                                                     \
-      d_ = fminf(fmaxf(d_, lo[NSJ] - lam[NSJ]), hi[NSJ] - lam[NSJ]);                                     \
+      d_ = fminf(fmaxf(d_, nlo), nhi);                                                                   \
       const float delta = gp.shfl(d_, row);                                                              \
       if (l == row) lam[NSJ] += delta;                                                                   \
       UG_CONTACT_APPLY(delta, 0.f, false, NACT)                                                          \
@@ -470,6 +513,21 @@ __device__ __noinline__ float solve_and_integrate(S& s, const DevModel& M, const
   }
   const int nact = (Rc + G - 1) / G;
   int it = 0;
+#if UG_JREG > 0
+  // Contact-free tick (about half of the ticks of the ball scenes: the arm moving before the paddle exists) with a
+  // warp per env: see joint_sweeps_reg. Instantiated for the two row counts that occur almost always (7 motors + 5
+  // gears, plus one active limit); anything else takes the generic sweeps below.
+  bool swept = false;
+  if constexpr (G == 32 && NSJ == 1) {
+    if (nact == 0 && (n_nc == UG_JREG || n_nc == UG_JREG + 1)) {
+      const unsigned a0 = aEj[0];
+      if (n_nc == UG_JREG) it = joint_sweeps_reg<UG_JREG>(s, gp, a0, rhs[0], invd[0], lo[0], hi[0], den[0], lam[0]);
+      else it = joint_sweeps_reg<UG_JREG + 1>(s, gp, a0, rhs[0], invd[0], lo[0], hi[0], den[0], lam[0]);
+      swept = true;
+    }
+  }
+  if (!swept)
+#endif
 #pragma unroll 1
   for (; it < UGP_SOLVER_ITERS;) {
     if (nact == 0) { UG_JOINT_SWEEP(0) }
@@ -482,8 +540,7 @@ __device__ __noinline__ float solve_and_integrate(S& s, const DevModel& M, const
     float res = 0.f;
 #pragma unroll
     for (int k = 0; k < NS; k++) { float r_ = (lam[k] - lamp[k]) * den[k]; res = fmaxf(res, r_ * r_); lamp[k] = lam[k]; }
-    res = gp.max(res);
-    if (res <= UGP_RESIDUAL_THRESHOLD) break;
+    if (!gp.any(res > UGP_RESIDUAL_THRESHOLD)) break;  // max over the rows <= threshold, as one vote
   }
 #undef UG_JOINT_STEP
 #undef UG_CONTACT_LOAD

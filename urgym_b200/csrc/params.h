@@ -34,3 +34,8 @@
 #define UGP_RESET_ARM_TICKS 10
 #define UGP_CLUB_ZC ((-0.09 + 0.08) / 3.0)
 #define UGP_PI 3.14159265358979323846f
+// contact-free ticks with this many joint rows, or one more, run the register-resident sweeps (0 disables them):
+// 7 motors + 5 gears = 12
+#ifndef UG_JREG
+#define UG_JREG 12
+#endif
