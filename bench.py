@@ -55,7 +55,7 @@ def peaks():
 
 
 def ncu_traffic(workload):
-    """(bytes per launch, issue-slot utilisation %) of the dominant kernel from the committed ncu capture, or (None, None)."""
+    """(DRAM bytes per gym step, issue-slot utilisation %) of env_kernel from the committed ncu capture, or (None, None)."""
     p = os.path.join(ROOT, 'profiles', 'ncu_traffic.json')
     if os.path.exists(p):
         with open(p) as f:
@@ -271,7 +271,7 @@ def main():
                 'ticks_per_env_step': float(gstats[0].item() / max(gstats[1].item(), 1)), 'physics_ticks_per_s': float(gstats[0].item() / (ms_total * 1e-3)),
                 'gpu_launches': int(l1 - l0), 'clocks': clk,
                 'roofline': {'bound': 'hbm', 'achieved': achieved, 'peak': peak, 'unit': 'GB/s', 'frac': achieved / peak,
-                             'traffic': traffic, 'traffic_unit': 'bytes per launch (ncu dram read + write; includes write-back of the L2-flush buffer)',
+                             'traffic': traffic, 'traffic_unit': 'bytes per gym step, summed over its env_kernel launches (ncu dram read + write; includes write-back of the L2-flush buffer)',
                              'algorithmic_bytes_per_launch': BYTES_PER_ENV_STEP[env] * n_envs, 'launches_per_step': (l1 - l0) / K,
                              'launch_note': 'one gym step = the env_kernel step grid, plus (ball scenes) the same kernel once more as a reset-only grid over the finished envs; achieved = bytes of the whole step / device time of the whole step',
                              'peak_source': how, 'kernel': 'env_kernel<%s>' % env, 'sm_issue_active_pct': issue_pct,

@@ -333,6 +333,27 @@ def test_reset_launch_scheduling_leaves_results_unchanged(name, monkeypatch):
             np.testing.assert_array_equal(x, y)
 
 
+@pytest.mark.parametrize('name', ['BallBalance', 'TwoBallsBalance', 'CubesGrasp'])
+def test_register_resident_sweeps_leave_results_unchanged(name, monkeypatch):
+    """Contact-free ticks with 12 or 13 joint rows run their PGS sweeps out of registers (dev_solver.cuh,
+    joint_sweeps_reg): same operations in the same order as the generic sweeps, so not a bit may differ."""
+    outs = []
+    for generic in ('1', '0'):
+        monkeypatch.setenv('URGYM_GENERIC_SWEEPS', generic)
+        gb = _batch(name, 1024, seed=29)
+        gb.reset()
+        rng = np.random.default_rng(14)
+        rec = [[_np(gb.obs).copy(), _np(gb.reset_ticks).copy()]]
+        for _ in range(6):
+            gb.step(_actions(rng, name, 1024), autoreset=True)
+            rec.append([_np(x).copy() for x in (gb.obs, gb.reward, gb.terminated, gb.truncated, gb.success, gb.final_obs, gb.nticks)])
+        rec.append([_np(gb.get_state()).copy()])
+        outs.append(rec)
+    for a, b in zip(outs[0], outs[1]):
+        for x, y in zip(a, b):
+            np.testing.assert_array_equal(x, y)
+
+
 @pytest.mark.parametrize('name', ['BallBalance', 'CubesGrasp', 'Golf'])
 def test_distributional_agreement_over_episodes(name):
     """Free-running (no re-synchronisation) rollouts diverge trajectory by trajectory — the dynamics are chaotic — but

@@ -1,9 +1,9 @@
 """Bit-level A/B of prebuilt libraries with the same ABI: same seeds, same actions, digest of everything a rollout returns.
 
-    python tools/ab_bits.py gpurun_ab/base.so urgym_b200/liburgym_b200.so [workload ...]
+    python tools/ab_bits.py gpurun_ab/base.so urgym_b200/liburgym_b200.so:URGYM_RESET_GROUP=16 [workload ...]
 
-Each library runs in its own process (URGYM_SO); a kernel change that claims "same operations, same order" must print
-identical digests.
+Each variant (library, optionally with environment settings after a colon, comma-separated) runs in its own process;
+a kernel change that claims "same operations, same order" must print identical digests.
 """
 import hashlib
 import os
@@ -38,13 +38,15 @@ if __name__ == '__main__':
     if sys.argv[1] == '--child':
         child(sys.argv[2], int(sys.argv[3]))
         sys.exit(0)
-    libs = [a for a in sys.argv[1:] if a.endswith('.so')]
-    wls = [a for a in sys.argv[1:] if not a.endswith('.so')] or ['ball4096', 'two16384', 'push16384', 'grasp16384', 'golf16384']
+    libs = [a for a in sys.argv[1:] if '.so' in a]
+    wls = [a for a in sys.argv[1:] if '.so' not in a] or ['ball4096', 'two16384', 'push16384', 'grasp16384', 'golf16384']
     bad = 0
     for w in wls:
         outs = []
         for so in libs:
-            env = dict(os.environ, URGYM_SO=os.path.abspath(so))
+            path, _, extra = so.partition(':')
+            env = dict(os.environ, URGYM_SO=os.path.abspath(path))
+            env.update(kv.split('=', 1) for kv in extra.split(',') if kv)
             r = subprocess.run([sys.executable, __file__, '--child', w, '12'], env=env, capture_output=True, text=True)
             outs.append(r.stdout.strip().splitlines()[-1] if r.returncode == 0 and r.stdout.strip() else 'FAILED ' + r.stderr[-300:])
         same = len(set(outs)) == 1

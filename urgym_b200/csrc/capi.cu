@@ -136,6 +136,7 @@ int urgym_create(int env_type, int num_envs, int device, uint64_t seed, int env_
   h->env_type = env_type; h->N = num_envs; h->device = device; h->seed = seed; h->gidx0 = env_index_offset; h->sparse = reward_sparse;
   h->split_reset = default_split_reset(env_type);
   if (build_model(env_type, &h->hmodel)) { delete h; return fail(URGYM_E_ARG, "model build failed"); }
+  { const char* e = getenv("URGYM_GENERIC_SWEEPS"); h->hmodel.generic_sweeps = e && atoi(e) != 0; }
   size_t n = (size_t)num_envs; int od = h->hmodel.obs_dim, ad = h->hmodel.act_dim;
   CK(cudaMalloc(&h->dmodel, sizeof(DevModel)));
   CK(cudaMemcpy(h->dmodel, &h->hmodel, sizeof(DevModel), cudaMemcpyHostToDevice));

@@ -519,7 +519,7 @@ __device__ __noinline__ float solve_and_integrate(S& s, const DevModel& M, const
   // gears, plus one active limit); anything else takes the generic sweeps below.
   bool swept = false;
   if constexpr (G == 32 && NSJ == 1) {
-    if (nact == 0 && (n_nc == UG_JREG || n_nc == UG_JREG + 1)) {
+    if (nact == 0 && (n_nc == UG_JREG || n_nc == UG_JREG + 1) && !M.generic_sweeps) {
       const unsigned a0 = aEj[0];
       if (n_nc == UG_JREG) it = joint_sweeps_reg<UG_JREG>(s, gp, a0, rhs[0], invd[0], lo[0], hi[0], den[0], lam[0]);
       else it = joint_sweeps_reg<UG_JREG + 1>(s, gp, a0, rhs[0], invd[0], lo[0], hi[0], den[0], lam[0]);

@@ -36,6 +36,7 @@ struct DevModel {
   float link_jquat[UG_NLINK][4]; float link_jxyz[UG_NLINK][3]; int link_parent[UG_NLINK]; int link_dof[UG_NLINK]; int link_axis[UG_NLINK];
   float aabb_c[2][3], aabb_h[2][3];  // collision AABBs of links 11 and 16 in their link frames
   int env_type, nfree, nshapes, npairs, obs_dim, act_dim, max_steps; float gravity;
+  int generic_sweeps;  // 1: contact-free ticks take the generic sweeps too (URGYM_GENERIC_SWEEPS=1 at create; comparison runs and tests)
   float fmass[UG_MAXFREE]; float finertia[UG_MAXFREE][3];
   DevShape shapes[UG_MAXSHAPES]; uint8_t pairs[UG_MAXPAIRS][2];
 };
