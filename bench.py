@@ -195,6 +195,12 @@ def main():
     torch.cuda.set_device(local)
     dev = torch.device('cuda', local)
     if world > 1:
+        # stdout carries exactly one JSON line: whatever native libraries print there (NCCL's "NCCL version ..." banner)
+        # goes to stderr; the line itself is written to the saved descriptor
+        sys.stdout.flush()
+        saved = os.dup(1)
+        os.dup2(2, 1)
+        sys.stdout = os.fdopen(saved, 'w')
         dist.init_process_group('nccl', device_id=dev)
 
     def barrier():
