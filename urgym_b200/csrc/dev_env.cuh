@@ -68,8 +68,10 @@ __device__ __noinline__ void ik_solve(const float* q_in, const DevModel& M, f3 t
   for (int it = 0; it < UGP_IK_ITERS && diff > UGP_IK_RESIDUAL; it++) {
     m3 R; f3 p = mk3(0, 0, 0);
     R.m[0] = 1; R.m[1] = 0; R.m[2] = 0; R.m[3] = 0; R.m[4] = 1; R.m[5] = 0; R.m[6] = 0; R.m[7] = 0; R.m[8] = 1;
+    // kept rolled: six inlined copies of this body (sincosf carries its range-reduction path) made the iteration a
+    // 2 k-instruction straight line that missed the instruction caches on every pass (profiles/, CubesPush)
     f3 axw[6], org[6];
-#pragma unroll
+#pragma unroll 1
     for (int d = 0; d < 6; d++) {
       p = p + mulv(R, ld3(M.jpos[d]));
       m3 R0 = mulm(R, ldm(M.jrot[d]));

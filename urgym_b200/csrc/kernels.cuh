@@ -10,9 +10,11 @@ template <int ENVF> struct Scene { static constexpr int value = ENVF == 5 ? 2 : 
 template <int ENVF> struct ObsDim { static constexpr int value = ENVF == 0 ? 6 : (ENVF == 3 ? 17 : (ENVF == 6 ? 15 : 9)); };
 template <int ENVF> struct ActDim { static constexpr int value = ENVF == 3 ? 9 : (ENVF == 6 ? 6 : 3); };
 
+// One out-of-line copy per env type (three call sites; the ball scenes' Euler conversion alone is ~0.9 k instructions):
+// once-per-step straight-line code is what the instruction caches miss on.
 template <int ENVF, class S>
-UG_DEV void observe(S& s, const DevModel& M, float* o, int lane) {
-  // caller guarantees fresh fk_bodies(); every lane computes, lane 0 writes
+__device__ __noinline__ void observe(S& s, const DevModel& M, float* o, float* o2, int lane) {
+  // caller guarantees fresh fk_bodies(); every lane computes, lane 0 writes (to o, and to o2 when given)
   constexpr int ENV = Scene<ENVF>::value;
   f3 ep; m3 eR; ee_pose(s, M, ep, eR);
   float v[17];
@@ -51,6 +53,10 @@ UG_DEV void observe(S& s, const DevModel& M, float* o, int lane) {
   if (lane == 0) {
 #pragma unroll
     for (int i = 0; i < OD; i++) o[i] = v[i];
+    if (o2) {
+#pragma unroll
+      for (int i = 0; i < OD; i++) o2[i] = v[i];
+    }
   }
 }
 
@@ -205,8 +211,7 @@ __global__ void __launch_bounds__(32, 13) env_kernel(KParams P) {
         if (lane < UG_MAXC) { P.contacts[((size_t)env * UG_MAXC + lane) * 2] = lane < nc ? (s.con[lane].shapes & 255) : -1; P.contacts[((size_t)env * UG_MAXC + lane) * 2 + 1] = lane < nc ? (s.con[lane].shapes >> 8) : -1; }
         if (lane == 0) P.ccount[env] = nc;
       }
-      observe<ENVF>(s, M, P.obs + (size_t)OD * env, lane);
-      if (P.final_obs) observe<ENVF>(s, M, P.final_obs + (size_t)OD * env, lane);
+      observe<ENVF>(s, M, P.obs + (size_t)OD * env, P.final_obs ? P.final_obs + (size_t)OD * env : nullptr, lane);
       if (lane == 0) { P.reward[env] = rew; P.term[env] = term; P.trunc[env] = trunc; P.succ[env] = succ; }
       if ((term || trunc) && lane == 0 && P.stats) {
         atomicAdd(&P.stats[0], 1.0); atomicAdd(&P.stats[1], (double)ep_ret); atomicAdd(&P.stats[2], (double)step_count); atomicAdd(&P.stats[3], succ ? 1.0 : 0.0);
@@ -275,7 +280,7 @@ __global__ void __launch_bounds__(32, 13) env_kernel(KParams P) {
       continue;
     }
     // PH_SETTLE2: reset finished -> first observation of the new episode
-    observe<ENVF>(s, M, P.obs + (size_t)OD * env, lane);
+    observe<ENVF>(s, M, P.obs + (size_t)OD * env, nullptr, lane);
     break;
   }
   if (P.nticks) {
