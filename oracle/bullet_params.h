@@ -36,11 +36,27 @@
 #define BP_IK_DAMPING 0.5                 // default per-joint damping added to the diagonal of J^T J
 #define BP_IK_RESIDUAL 1e-4               // default residualThreshold (position error)
 #define BP_IK_MAX_STEP 0.7853981633974483 // BussIK MaxAngleDLS = 45 degrees
-// --- capacity choice of this implementation (not Bullet's): rolling-friction rows are built for the first 3 manifolds
-//     that carry rolling friction in a tick (Golf: ball on pitch + two club parts); a ball touching four things at once
-//     keeps normal and sliding friction on all of them
-#define BP_MAX_ROLLING_CONTACTS 3
 // --- settle loop given by the reference: env_ball_balance_v0.py:94-103
 #define BP_SETTLE_MAX_TICKS 480
 #define BP_SETTLE_THRESHOLD 5e-3
 #define BP_RESET_ARM_TICKS 10             // robot.py:97-98
+
+// --- run-time copies of the recalled values, so that tools/ablate_params.py can ask how sensitive the replay of the
+//     reference's pybullet-trained actors is to each of them. Defaults are the macros above; nothing else
+//     changes them.
+struct BulletParams {
+  double erp = BP_ERP, erp2 = BP_ERP2, linear_slop = BP_LINEAR_SLOP, restitution_threshold = BP_RESTITUTION_VEL_THRESHOLD;
+  double lin_damping = BP_LIN_DAMPING, ang_damping = BP_ANG_DAMPING, contact_breaking = BP_CONTACT_BREAKING;
+  double motor_kp = BP_MOTOR_KP, motor_kd = BP_MOTOR_KD, ik_damping = BP_IK_DAMPING, max_friction = BP_MAX_FRICTION;
+  double solver_iters = BP_SOLVER_ITERS;
+  double robot_mu = 0.5;        // URDF links without <contact> coefficients [recalled default 0.5]
+  double body_mu = 0.5;         // createMultiBody bodies (paddle, balls, table, pitch, club parts) [recalled default 0.5]
+  double cube_mu = 1.0;         // cube.urdf lateral_friction [recalled]
+  double plane_mu = 1.0;        // plane.urdf lateral_friction [recalled]
+  double cube_mass = 1.0;       // cube.urdf mass under globalScaling=0.04 [recalled: mass not scaled]
+  double friction_cone = 1.0;   // 1: implicit cone over the two tangent rows; 0: independent box limits per row
+  double roll_points = 1.0;     // rolling-friction rows on the first `roll_points` points of a manifold
+  double link_mask = 524287.0;  // ablation: bit i = robot link i collides (all 19 by default)
+  double box_shrink = 0.0;      // ablation: metres taken off every half extent of the fitted robot link boxes
+};
+inline BulletParams& bp() { static BulletParams p; return p; }

@@ -11,6 +11,12 @@
 
 namespace urgo {
 
+// Smallest |x| over every inequality `x > 0` the narrowphase has decided since the caller last reset it (separating-axis
+// tests against the margin, clip keep tests, sphere distance tests): how close the contact SET of a tick came to being a
+// different one. Tests read it to tell an fp32 threshold flip from a disagreement (tests/test_gpu_parity.py).
+inline double& decision_margin() { static thread_local double m = 1e300; return m; }
+inline void note_decision(double x) { double a = std::fabs(x); if (a < decision_margin()) decision_margin() = a; }
+
 struct BoxW { V3 c; M3 R; V3 h; };
 // normal n points from B to A; posA = posB + n * dist; dist < 0 is penetration
 struct CPoint { V3 posA, posB, n; double dist; };
@@ -54,6 +60,7 @@ inline int box_box(const BoxW& A, const BoxW& B, double margin, CPoint out[4]) {
     double e1 = pp[i];
     double e2 = A.h[i] + B.h[0] * Q[i][0] + B.h[1] * Q[i][1] + B.h[2] * Q[i][2];
     double s = std::fabs(e1) - e2;
+    note_decision(s - margin);
     if (s > margin) return 0;
     if (s > best) { best = s; nrm = A.R.col(i); invert = e1 < 0; code = 1 + i; }
   }
@@ -61,6 +68,7 @@ inline int box_box(const BoxW& A, const BoxW& B, double margin, CPoint out[4]) {
     double e1 = dot(B.R.col(j), p);
     double e2 = A.h[0] * Q[0][j] + A.h[1] * Q[1][j] + A.h[2] * Q[2][j] + B.h[j];
     double s = std::fabs(e1) - e2;
+    note_decision(s - margin);
     if (s > margin) return 0;
     if (s > best) { best = s; nrm = B.R.col(j); invert = e1 < 0; code = 4 + j; }
   }
@@ -75,6 +83,7 @@ inline int box_box(const BoxW& A, const BoxW& B, double margin, CPoint out[4]) {
       double e1 = dot(pp, L);
       double e2 = A.h[i1] * Q[i2][j] + A.h[i2] * Q[i1][j] + B.h[j1] * Q[i][j2] + B.h[j2] * Q[i][j1];
       double s = (std::fabs(e1) - e2) / l;
+      note_decision(s - margin);
       if (s > margin) return 0;
       if (edge_bias(s) > best) { best = s; nrm = A.R * (L * (1.0 / l)); invert = e1 < 0; code = 7 + 3 * i + j; }
     }
@@ -115,6 +124,7 @@ inline int box_box(const BoxW& A, const BoxW& B, double margin, CPoint out[4]) {
   int keep[16], m = 0; double dep[16];
   for (int v = 0; v < n; v++) {
     double dv = ref.h[k] - clipped[v][2];
+    note_decision(dv + margin);
     if (dv >= -margin) { keep[m] = v; dep[m] = dv; m++; }
   }
   if (m == 0) return 0;
@@ -156,6 +166,7 @@ inline bool sphere_box(V3 sc, double r, const BoxW& B, double margin, V3& on_box
     cl = l; cl[ax] = nl[ax] * B.h[ax];
     dist = -md - r;
   }
+  note_decision(dist - margin);
   if (!(dist < margin)) return false;
   on_box = B.c + B.R * cl;
   n_box_to_sphere = B.R * nl;

@@ -21,13 +21,16 @@ enum { ENV_BALL = 0, ENV_TWO = 1, ENV_PUSH = 2, ENV_GRASP = 3, ENV_GOLF = 4, ENV
 // env_cubes_push_diff_v0.py:209-211 (cube positions relative to the end effector), env_golf_joints_v0.py:60-63,85,123-124,229-234
 // (six joint displacements instead of an end-effector displacement; the six arm joints prepended to the observation).
 inline int scene_of(int env_type) { return env_type == ENV_PUSH_DIFF ? ENV_PUSH : (env_type == ENV_GOLF_JOINTS ? ENV_GOLF : env_type); }
-enum { NDOF = 12, NMOTOR = 7, MAXFREE = 3, MAXC = 16, STATE_SLOTS = 96 };
+// The oracle keeps every manifold point and every rolling-friction row (Bullet has no global cap, only 4 points per
+// manifold). EXPORT_MAXC is the width of the contact-pair export only (urgo_contacts).
+enum { NDOF = 12, NMOTOR = 7, MAXFREE = 3, EXPORT_MAXC = 64, STATE_SLOTS = 96 };
 // Movable joints in Bullet link numbering; env code agrees (robot.py:68-73, first six = arm).
 static const int MOV[NDOF] = {1, 2, 3, 4, 5, 6, 9, 11, 13, 14, 16, 18};
 // Gear rows: parent finger_joint (link 9, dof 6) with each mimic child; gearRatio = -multiplier (robot.py:190-211).
 static const int GEAR_DOF[5] = {7, 8, 9, 10, 11};            // links 11, 13, 14, 16, 18
 static const double GEAR_RATIO[5] = {1.0, -1.0, -1.0, 1.0, -1.0};
-// Order in which robot links enter the pair list (pads and fingers first so the contact cap never drops them).
+// Order in which robot links enter the pair list, and so the order of the contact rows inside a Gauss-Seidel sweep
+// (Bullet's own order is that of its manifold array, i.e. of broadphase pair creation: arbitrary). Gripper first.
 static const int LINK_ORDER[17] = {12, 17, 11, 16, 10, 15, 9, 14, 13, 18, 8, 6, 5, 4, 3, 2, 1};
 
 struct ShapeDef {
@@ -49,11 +52,11 @@ struct Scene {
 
 inline ShapeDef mk_box(int body, int link, V3 lc, V3 half, double mu, double rest = 0, double roll = 0) {
   ShapeDef s; s.kind = 0; s.body = body; s.link = link; s.lc = lc; s.lR = M3::identity(); s.half = half; s.radius = 0;
-  s.mu = mu; s.rest = rest; s.roll = roll; s.cbt = BP_CONTACT_BREAKING * norm(half); return s;
+  s.mu = mu; s.rest = rest; s.roll = roll; s.cbt = bp().contact_breaking * norm(half); return s;
 }
 inline ShapeDef mk_sphere(int body, int link, double r, double mu, double rest = 0, double roll = 0) {
   ShapeDef s; s.kind = 1; s.body = body; s.link = link; s.lc = V3(); s.lR = M3::identity(); s.half = V3(r, r, r); s.radius = r;
-  s.mu = mu; s.rest = rest; s.roll = roll; s.cbt = BP_CONTACT_BREAKING * r; return s;
+  s.mu = mu; s.rest = rest; s.roll = roll; s.cbt = bp().contact_breaking * r; return s;
 }
 inline V3 box_inertia(double m, V3 h) {
   double lx = 2 * h.x, ly = 2 * h.y, lz = 2 * h.z;
@@ -69,42 +72,52 @@ inline Scene make_scene(int env_type_full) {
   for (int k = 0; k < 17; k++) {  // robot link boxes (link 0 rests on the table and link 7's 1 cm box is interior)
     const UrgLinkModel& L = URG_LINKS[LINK_ORDER[k]];
     ShapeDef s = mk_box(0, LINK_ORDER[k], V3(L.box_center[0], L.box_center[1], L.box_center[2]),
-                        V3(L.box_half[0], L.box_half[1], L.box_half[2]), 0.5);
+                        V3(L.box_half[0], L.box_half[1], L.box_half[2]), bp().robot_mu);
     for (int i = 0; i < 9; i++) s.lR.m[i] = L.box_rot[i];
+    if (!(((long)bp().link_mask >> LINK_ORDER[k]) & 1)) s.half = V3(1e-6, 1e-6, 1e-6);  // ablation: link does not collide
+    else if (bp().box_shrink > 0 && LINK_ORDER[k] != 12 && LINK_ORDER[k] != 17) s.half = V3(std::fmax(s.half.x - bp().box_shrink, 1e-4), std::fmax(s.half.y - bp().box_shrink, 1e-4), std::fmax(s.half.z - bp().box_shrink, 1e-4));
     sc.shapes.push_back(s);
   }
   const V3 table_c(0, 0, -0.25), table_h(0.5, 1.0, 0.25);  // env_ball_balance_v0.py:69-71
+  const double bm = bp().body_mu, cm = bp().cube_mu, cmass = bp().cube_mass;
+  // plane.urdf (30 x 30 x 10 box collider, 5 m below its origin, friction 1 [recalled]) at z = -0.5 under the table
+  // (env_ball_balance_v0.py:70, env_cubes_push_v0.py:77, env_golf_v0.py:77); static id 2. Whatever leaves the table
+  // comes to rest on it instead of falling for the rest of the episode.
+  const ShapeDef ground = mk_box(-1, 2, V3(0, 0, -0.5 - 5.0), V3(15, 15, 5), bp().plane_mu);
   switch (env_type) {
     case ENV_BALL:  // env_ball_balance_v0.py:177-203
       sc.nfree = 2; sc.obs_dim = 6; sc.act_dim = 3; sc.max_steps = 500;
       sc.fmass[0] = 0.1; sc.finertia[0] = box_inertia(0.1, V3(0.05, 0.1, 0.005));
       sc.fmass[1] = 0.01; sc.finertia[1] = V3(1, 1, 1) * (0.4 * 0.01 * 0.02 * 0.02);
-      sc.shapes.push_back(mk_box(1, -1, V3(), V3(0.05, 0.1, 0.005), 0.5));
-      sc.shapes.push_back(mk_sphere(2, -1, 0.02, 0.5));
-      sc.shapes.push_back(mk_box(-1, 0, table_c, table_h, 0.5));
+      sc.shapes.push_back(mk_box(1, -1, V3(), V3(0.05, 0.1, 0.005), bm));
+      sc.shapes.push_back(mk_sphere(2, -1, 0.02, bm));
+      sc.shapes.push_back(mk_box(-1, 0, table_c, table_h, bm));
+      sc.shapes.push_back(ground);
       break;
     case ENV_TWO:  // env_two_balls_balance_v0.py:187,200-233
       sc.nfree = 3; sc.obs_dim = 9; sc.act_dim = 3; sc.max_steps = 500;
       sc.fmass[0] = 0.1; sc.finertia[0] = box_inertia(0.1, V3(0.05, 0.1, 0.005));
       for (int b = 1; b < 3; b++) { sc.fmass[b] = 0.01; sc.finertia[b] = V3(1, 1, 1) * (0.4 * 0.01 * 0.003 * 0.003); }
-      sc.shapes.push_back(mk_box(1, -1, V3(), V3(0.05, 0.1, 0.005), 0.5));
-      sc.shapes.push_back(mk_sphere(2, -1, 0.003, 0.5));
-      sc.shapes.push_back(mk_sphere(3, -1, 0.003, 0.5));
-      sc.shapes.push_back(mk_box(-1, 0, table_c, table_h, 0.5));
+      sc.shapes.push_back(mk_box(1, -1, V3(), V3(0.05, 0.1, 0.005), bm));
+      sc.shapes.push_back(mk_sphere(2, -1, 0.003, bm));
+      sc.shapes.push_back(mk_sphere(3, -1, 0.003, bm));
+      sc.shapes.push_back(mk_box(-1, 0, table_c, table_h, bm));
+      sc.shapes.push_back(ground);
       break;
     case ENV_PUSH:  // env_cubes_push_v0.py:233-246; cube.urdf: unit box, mass 1, lateral friction 1 [recalled]
       sc.nfree = 2; sc.obs_dim = 9; sc.act_dim = 3; sc.max_steps = 50;
       for (int b = 0; b < 2; b++) {
-        sc.fmass[b] = 1.0; sc.finertia[b] = box_inertia(1.0, V3(0.02, 0.02, 0.02));
-        sc.shapes.push_back(mk_box(b + 1, -1, V3(), V3(0.02, 0.02, 0.02), 1.0));
+        sc.fmass[b] = cmass; sc.finertia[b] = box_inertia(cmass, V3(0.02, 0.02, 0.02));
+        sc.shapes.push_back(mk_box(b + 1, -1, V3(), V3(0.02, 0.02, 0.02), cm));
       }
-      sc.shapes.push_back(mk_box(-1, 0, table_c, table_h, 0.5));
+      sc.shapes.push_back(mk_box(-1, 0, table_c, table_h, bm));
+      sc.shapes.push_back(ground);
       break;
     case ENV_GRASP:  // env_cubes_grasp_v0.py:43,48,305; plane.urdf: 30x30x10 box 5 m below origin, friction 1 [recalled]
       sc.nfree = 1; sc.obs_dim = 17; sc.act_dim = 9; sc.max_steps = 20; sc.gravity = -10.0;
-      sc.fmass[0] = 1.0; sc.finertia[0] = box_inertia(1.0, V3(0.02, 0.02, 0.02));
-      sc.shapes.push_back(mk_box(1, -1, V3(), V3(0.02, 0.02, 0.02), 1.0));
-      sc.shapes.push_back(mk_box(-1, 0, V3(0, 0, -5.0), V3(15, 15, 5), 1.0));
+      sc.fmass[0] = cmass; sc.finertia[0] = box_inertia(cmass, V3(0.02, 0.02, 0.02));
+      sc.shapes.push_back(mk_box(1, -1, V3(), V3(0.02, 0.02, 0.02), cm));
+      sc.shapes.push_back(mk_box(-1, 0, V3(0, 0, -5.0), V3(15, 15, 5), bp().plane_mu));
       break;
     case ENV_GOLF: {  // env_golf_v0.py:87,289-358
       sc.nfree = 2; sc.obs_dim = 9; sc.act_dim = 3; sc.max_steps = 100;
@@ -116,11 +129,12 @@ inline Scene make_scene(int env_type_full) {
       sc.finertia[0] = V3(ib.x + it.x + id.x + d0 * d0 + d1 * d1 + d2 * d2, ib.y + it.y + id.y + d0 * d0 + d1 * d1 + d2 * d2, ib.z + it.z + id.z);
       sc.fmass[1] = 0.01; sc.finertia[1] = V3(1, 1, 1) * (0.4 * 0.01 * 0.015 * 0.015);
       sc.shapes.push_back(mk_box(1, -1, V3(0, 0, d0), V3(0.015, 0.015, 0.075), 10.0, 0.1));
-      sc.shapes.push_back(mk_box(1, 0, V3(0, 0, d1), V3(0.05, 0.015, 0.015), 0.5));
-      sc.shapes.push_back(mk_box(1, 1, V3(0, 0, d2), V3(0.04, 0.04, 0.005), 0.5));  // disc r=0.04 h=0.01 as a box
-      sc.shapes.push_back(mk_sphere(2, -1, 0.015, 0.5, 0.1, 10.0));
-      sc.shapes.push_back(mk_box(-1, 0, table_c, table_h, 0.5));
-      sc.shapes.push_back(mk_box(-1, 1, V3(0, -0.6, 0.02), V3(URG_PITCH_HALF[0], URG_PITCH_HALF[1], URG_PITCH_HALF[2]), 0.5));
+      sc.shapes.push_back(mk_box(1, 0, V3(0, 0, d1), V3(0.05, 0.015, 0.015), bm));
+      sc.shapes.push_back(mk_box(1, 1, V3(0, 0, d2), V3(0.04, 0.04, 0.005), bm));  // disc r=0.04 h=0.01 as a box
+      sc.shapes.push_back(mk_sphere(2, -1, 0.015, bm, 0.1, 10.0));
+      sc.shapes.push_back(mk_box(-1, 0, table_c, table_h, bm));
+      sc.shapes.push_back(mk_box(-1, 1, V3(0, -0.6, 0.02), V3(URG_PITCH_HALF[0], URG_PITCH_HALF[1], URG_PITCH_HALF[2]), bm));
+      sc.shapes.push_back(ground);
       break;
     }
   }
@@ -226,8 +240,8 @@ struct Robot {
       M3 Ic = rot_diag(R[i], V3(L.inertia[0], L.inertia[1], L.inertia[2]));
       IA[i] = spatial_inertia(L.mass, com[i], Ic);
       V3 w = top(v[i]), vc = bot(v[i]) + cross(w, com[i]);
-      V3 f = V3(0, 0, L.mass * gz) - vc * (L.mass * (BP_LIN_DAMPING + BP_LIN_DAMPING * norm(vc)));
-      V3 tq = -1.0 * ((Ic * w) * (BP_ANG_DAMPING + BP_ANG_DAMPING * norm(w)));
+      V3 f = V3(0, 0, L.mass * gz) - vc * (L.mass * (bp().lin_damping + bp().lin_damping * norm(vc)));
+      V3 tq = -1.0 * ((Ic * w) * (bp().ang_damping + bp().ang_damping * norm(w)));
       S6 fext = s6(tq + cross(com[i], f), f);
       pA[i] = crf(v[i], mul(IA[i], v[i])) - fext;
     }
@@ -296,7 +310,7 @@ struct World {
   std::vector<Contact> contacts;
   int last_iters = 0;
   long st_ticks = 0, st_iters = 0, st_rows = 0, st_contacts = 0, st_rowiters = 0;  // profiling counters (tests / design notes)
-  long st_hist_rows[96] = {0}, st_hist_nc[24] = {0}, st_hist_nnc[32] = {0};
+  long st_hist_rows[192] = {0}, st_hist_nc[64] = {0}, st_hist_nnc[32] = {0}, st_hist_roll[16] = {0};
 
   explicit World(int env_type) : sc(make_scene(env_type)) { for (int i = 0; i < NMOTOR; i++) target[i] = 0; }
 
@@ -309,10 +323,11 @@ struct World {
   }
   bool shape_active(const ShapeDef& s) const { return s.body <= 0 || fb[s.body - 1].active; }
 
+  double contact_margin = 1e300;  // decision_margin() of the last collide()
   void collide() {
     contacts.clear();
+    decision_margin() = 1e300;
     for (auto& pr : sc.pairs) {
-      if ((int)contacts.size() >= MAXC) break;
       const ShapeDef& A = sc.shapes[pr.first]; const ShapeDef& B = sc.shapes[pr.second];
       if (!shape_active(A) || !shape_active(B)) continue;
       double margin = std::fmin(A.cbt, B.cbt);
@@ -328,20 +343,22 @@ struct World {
         if (sphere_box(b.c, B.radius, a, margin, oa, na, d)) { pts[0].n = -na; pts[0].dist = d; pts[0].posA = oa; pts[0].posB = oa + na * d; n = 1; }
       } else {
         V3 dv = a.c - b.c; double len = norm(dv); double d = len - A.radius - B.radius;
+        note_decision(d - margin);
         if (d < margin) {
           V3 nn = len > 1e-12 ? dv * (1.0 / len) : V3(1, 0, 0);
           pts[0].n = nn; pts[0].dist = d; pts[0].posB = b.c + nn * B.radius; pts[0].posA = pts[0].posB + nn * d; n = 1;
         }
       }
-      for (int i = 0; i < n && (int)contacts.size() < MAXC; i++) {
+      for (int i = 0; i < n; i++) {
         Contact c; c.sa = pr.first; c.sb = pr.second; c.posA = pts[i].posA; c.posB = pts[i].posB; c.n = pts[i].n; c.dist = pts[i].dist;
-        c.mu = std::fmax(-BP_MAX_FRICTION, std::fmin(BP_MAX_FRICTION, A.mu * B.mu));
+        c.mu = std::fmax(-bp().max_friction, std::fmin(bp().max_friction, A.mu * B.mu));
         c.rest = A.rest * B.rest;
-        c.roll = std::fmax(-BP_MAX_FRICTION, std::fmin(BP_MAX_FRICTION, A.roll * B.mu + B.roll * A.mu));
-        if (i > 0) c.roll = 0;  // only the first point of a manifold gets rolling-friction rows [recalled]
+        c.roll = std::fmax(-bp().max_friction, std::fmin(bp().max_friction, A.roll * B.mu + B.roll * A.mu));
+        if (i >= (int)bp().roll_points) c.roll = 0;  // only the first point of a manifold gets rolling-friction rows [recalled]
         contacts.push_back(c);
       }
     }
+    contact_margin = decision_margin();
   }
 
   // side of a row for one shape: direction dir at point P (lin) or pure torque dir (!lin), scaled by sgn
@@ -409,11 +426,11 @@ struct World {
       if (!fb[b].active) continue;
       FreeBody& B = fb[b];
       M3 R = quat_to_mat(B.quat);
-      V3 acc = V3(0, 0, sc.gravity) - B.lin * (BP_LIN_DAMPING + BP_LIN_DAMPING * norm(B.lin));
+      V3 acc = V3(0, 0, sc.gravity) - B.lin * (bp().lin_damping + bp().lin_damping * norm(B.lin));
       V3 wl = tmul(R, B.ang);
       V3 I = sc.finertia[b];
       V3 Iw(I.x * wl.x, I.y * wl.y, I.z * wl.z);
-      V3 tq = -1.0 * (Iw * (BP_ANG_DAMPING + BP_ANG_DAMPING * norm(wl))) - cross(wl, Iw);
+      V3 tq = -1.0 * (Iw * (bp().ang_damping + bp().ang_damping * norm(wl))) - cross(wl, Iw);
       V3 al(tq.x / I.x, tq.y / I.y, tq.z / I.z);
       B.lin += acc * dt; B.ang += (R * al) * dt;
     }
@@ -428,7 +445,7 @@ struct World {
         r.Jr[d] = side == 0 ? 1.0 : -1.0;
         finish_row(r);
         double rel = row_vel(r, rob.qd);
-        r.rhs = (-pen * BP_ERP / dt - rel) * r.invd; r.lo = 0; r.hi = BP_LIMIT_MAX_IMPULSE;
+        r.rhs = (-pen * bp().erp / dt - rel) * r.invd; r.lo = 0; r.hi = BP_LIMIT_MAX_IMPULSE;
         nc.push_back(r);
       }
     }
@@ -438,7 +455,7 @@ struct World {
       Row r; r.has_robot = true; for (int k = 0; k < NDOF; k++) r.Jr[k] = 0;
       r.Jr[m] = 1.0;
       finish_row(r);
-      double want = BP_MOTOR_KP * (target[m] - rob.q[m]) / dt + (1.0 - BP_MOTOR_KD) * rob.qd[m];
+      double want = bp().motor_kp * (target[m] - rob.q[m]) / dt + (1.0 - bp().motor_kd) * rob.qd[m];
       want = std::fmax(-L.velocity, std::fmin(L.velocity, want));
       r.rhs = (want - rob.qd[m]) * r.invd; r.lo = -L.effort * dt; r.hi = L.effort * dt;
       nc.push_back(r);
@@ -449,7 +466,7 @@ struct World {
       finish_row(r);
       double rel = row_vel(r, rob.qd);
       double pos_err = BP_GEAR_ERP * (rob.q[6] + GEAR_RATIO[g] * rob.q[GEAR_DOF[g]]);
-      r.rhs = (-pos_err * BP_ERP / dt - rel) * r.invd; r.lo = -BP_GEAR_MAX_FORCE * dt; r.hi = BP_GEAR_MAX_FORCE * dt;
+      r.rhs = (-pos_err * bp().erp / dt - rel) * r.invd; r.lo = -BP_GEAR_MAX_FORCE * dt; r.hi = BP_GEAR_MAX_FORCE * dt;
       nc.push_back(r);
     }
     for (size_t ci = 0; ci < contacts.size(); ci++) {  // contacts (rows P5, P6)
@@ -457,15 +474,15 @@ struct World {
       const ShapeDef& A = sc.shapes[c.sa]; const ShapeDef& B = sc.shapes[c.sb];
       Row n; add_side(n, A, c.posA, c.n, true, 1.0); add_side(n, B, c.posB, c.n, true, -1.0); finish_row(n);
       double rel = row_vel(n, rob.qd);
-      double pen = c.dist + BP_LINEAR_SLOP;
+      double pen = c.dist + bp().linear_slop;
       double rest = 0;
-      if (std::fabs(rel) >= BP_RESTITUTION_VEL_THRESHOLD) { rest = c.rest * -rel; if (rest < 0) rest = 0; }
+      if (std::fabs(rel) >= bp().restitution_threshold) { rest = c.rest * -rel; if (rest < 0) rest = 0; }
       double pos_e = 0, vel_e = rest - rel;
-      if (pen > 0) vel_e -= pen / dt; else pos_e = -pen * BP_ERP2 / dt;
+      if (pen > 0) vel_e -= pen / dt; else pos_e = -pen * bp().erp2 / dt;
       n.rhs = (pos_e + vel_e) * n.invd; n.lo = 0; n.hi = 1e10;
       int nidx = (int)nr.size(); nr.push_back(n);
       V3 t1, t2; plane_space(c.n, t1, t2);
-      if (c.roll > 0 && (int)tr.size() < 2 * BP_MAX_ROLLING_CONTACTS) {
+      if (c.roll > 0) {
         for (int k = 0; k < 2; k++) {
           Row t; V3 dir = k == 0 ? t1 : t2;
           add_side(t, A, c.posA, dir, false, 1.0); add_side(t, B, c.posB, dir, false, -1.0); finish_row(t);
@@ -481,7 +498,7 @@ struct World {
     // --- projected Gauss-Seidel, Bullet's sweep order (row P6)
     DV dv; for (int d = 0; d < NDOF; d++) dv.r[d] = 0;
     int it = 0;
-    for (; it < BP_SOLVER_ITERS; it++) {
+    for (; it < (int)bp().solver_iters; it++) {
       double res = 0;
       int nn = (int)nc.size();
       for (int j = 0; j < nn; j++) { int idx = (it & 1) ? j : nn - 1 - j; double r = resolve(nc[idx], dv); res = std::fmax(res, r * r); }
@@ -493,6 +510,12 @@ struct World {
       for (size_t j = 0; j + 1 < fr.size(); j += 2) {  // implicit friction cone over the two tangent rows [recalled]
         Row& a = fr[j]; Row& b = fr[j + 1];
         double lim = a.mu * nr[a.nidx].applied;
+        if (bp().friction_cone == 0.0) {  // ablation: independent box limits, row after row
+          a.lo = -lim; a.hi = lim; b.lo = -lim; b.hi = lim;
+          double x = resolve(a, dv), y = resolve(b, dv);
+          res = std::fmax(res, std::fmax(x * x, y * y));
+          continue;
+        }
         double da = a.rhs - row_dv(a, dv) * a.invd, db = b.rhs - row_dv(b, dv) * b.invd;
         double sa = a.applied + da, sb = b.applied + db;
         if (sa < -lim || sa > lim || sb < -lim || sb > lim) {
@@ -508,7 +531,7 @@ struct World {
       if (res <= BP_RESIDUAL_THRESHOLD) { it++; break; }
     }
     last_iters = it;
-    { long R = (long)(nc.size() + nr.size() + tr.size() + fr.size()); st_ticks++; st_iters += it; st_rows += R; st_contacts += (long)contacts.size(); st_rowiters += R * it; st_hist_rows[R < 95 ? R : 95]++; st_hist_nc[contacts.size() < 23 ? contacts.size() : 23]++; st_hist_nnc[nc.size() < 31 ? nc.size() : 31]++; }
+    { long R = (long)(nc.size() + nr.size() + tr.size() + fr.size()); st_ticks++; st_iters += it; st_rows += R; st_contacts += (long)contacts.size(); st_rowiters += R * it; st_hist_rows[R < 191 ? R : 191]++; st_hist_nc[contacts.size() < 63 ? contacts.size() : 63]++; st_hist_roll[tr.size() / 2 < 15 ? tr.size() / 2 : 15]++; st_hist_nnc[nc.size() < 31 ? nc.size() : 31]++; }
     // --- apply and integrate (semi-implicit Euler; exponential map for free-body orientation)
     for (int d = 0; d < NDOF; d++) {
       rob.qd[d] = std::fmax(-BP_MAX_COORD_VEL, std::fmin(BP_MAX_COORD_VEL, rob.qd[d] + dv.r[d]));
@@ -555,7 +578,7 @@ struct World {
       }
       double A[6][7];
       for (int a = 0; a < 6; a++) {
-        for (int b = 0; b < 6; b++) { double s = 0; for (int k = 0; k < 6; k++) s += J[k][a] * J[k][b]; A[a][b] = s + (a == b ? BP_IK_DAMPING : 0.0); }
+        for (int b = 0; b < 6; b++) { double s = 0; for (int k = 0; k < 6; k++) s += J[k][a] * J[k][b]; A[a][b] = s + (a == b ? bp().ik_damping : 0.0); }
         double s = 0; for (int k = 0; k < 6; k++) s += J[k][a] * e[k]; A[a][6] = s;
       }
       for (int a = 0; a < 6; a++) {  // Gaussian elimination with partial pivoting

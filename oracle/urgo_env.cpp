@@ -10,8 +10,10 @@
 // /root/reference/urgym/envs/__init__.py:10-44 (the TimeLimit wrapper's `truncated`).
 //
 // Only tests/, __graft_entry__.smoke() and bench.py's cpu_baseline / --impl reference legs may load this library.
+#include <algorithm>
 #include <cstdio>
 #include <initializer_list>
+#include <string>
 
 #include "urgo_engine.h"
 
@@ -45,7 +47,7 @@ struct Env {
   bool approached = false, grasped = false;
   Q4 vertical;
   bool sparse = false;
-  int last_contacts[MAXC][2]; int last_ncontacts = 0;
+  std::vector<std::pair<int, int>> last_contacts;
   long total_ticks = 0;
   // command trace for the env-logic parity tests: events of 9 doubles {code, v[8]} (tests/golden/make_golden.py)
   bool tracing = false; std::vector<double> trace;
@@ -59,12 +61,15 @@ struct Env {
   Env(int t, uint64_t s, uint32_t g) : w(t), env_type(scene_of(t)), seed(s), gidx(g), variant(t) {}
 
   static bool settled(double l1_motion) { return l1_motion < BP_SETTLE_THRESHOLD; }
+  std::vector<double> settle_l1;  // summed joint motion of every tick of the last settle() (decision margins for the tests)
   int settle() {  // wait_until_stable, e.g. env_ball_balance_v0.py:94-103
     double prev[NDOF]; std::memcpy(prev, w.rob.q, sizeof(prev));
     int n = 0;
+    settle_l1.clear();
     for (; n < BP_SETTLE_MAX_TICKS;) {
       w.tick(); n++;
       double s = 0; for (int d = 0; d < NDOF; d++) s += std::fabs(prev[d] - w.rob.q[d]);
+      settle_l1.push_back(s);
       if (settled(s)) break;
       std::memcpy(prev, w.rob.q, sizeof(prev));
     }
@@ -107,12 +112,14 @@ struct Env {
   int reset(const double* ov, double* obs) {
     episode++; step_count = 0; approached = grasped = false;
     int ticks = 0;
-    for (int b = 0; b < MAXFREE; b++) w.fb[b].active = false;
+    // robot.reset() runs first, with the previous episode's objects still in the world (e.g. env_ball_balance_v0.py:147-152,
+    // env_cubes_push_v0.py:214-215 + 238-241, env_golf_v0.py:240-248): they are removed after the ten arm ticks
     for (int i = 0; i < 6; i++) { w.rob.q[i] = REST_POSE[i]; w.rob.qd[i] = 0; }   // robot.py:93-94
     ev(EV_RESET_ARM, {REST_POSE[0], REST_POSE[1], REST_POSE[2], REST_POSE[3], REST_POSE[4], REST_POSE[5]});
     for (int i = 0; i < BP_RESET_ARM_TICKS; i++) { w.tick(); ticks++; total_ticks++; }  // robot.py:97-98
     ev(EV_TICKS, {(double)BP_RESET_ARM_TICKS});
     move_gripper(0.085);                                                            // robot.py:100-101
+    for (int b = 0; b < MAXFREE; b++) w.fb[b].active = false;                       // removeBody of the old task objects
     V3 ep; Q4 eq;
     switch (env_type) {
       case ENV_BALL: case ENV_TWO: {
@@ -251,7 +258,8 @@ struct Env {
         break;
       }
       case ENV_PUSH: {
-        bool table = touch([](const ShapeDef& A, const ShapeDef& B, void*) { return A.body == 0 && B.body < 0 && A.link != 0; });
+        // getContactPoints(robot, table) (env_cubes_push_v0.py:176-183): the table only, not the ground plane under it
+        bool table = touch([](const ShapeDef& A, const ShapeDef& B, void*) { return A.body == 0 && B.body < 0 && B.link == 0 && A.link != 0; });
         bool fingers = touch([](const ShapeDef& A, const ShapeDef& B, void*) { return A.body == 0 && B.body == 2 && A.link >= 9 && A.link <= 18; });
         if (table) { rew -= 0.01; }
         else if (fingers) {
@@ -298,8 +306,8 @@ struct Env {
         break;
       }
     }
-    last_ncontacts = (int)w.contacts.size();
-    for (int i = 0; i < last_ncontacts; i++) { last_contacts[i][0] = w.contacts[i].sa; last_contacts[i][1] = w.contacts[i].sb; }
+    last_contacts.clear();
+    for (auto& c : w.contacts) last_contacts.push_back({c.sa, c.sb});
     step_count++;
     *reward = rew; *terminated = term; *success = succ; *truncated = step_count >= w.sc.max_steps;
     observe(obs);
@@ -399,14 +407,16 @@ int urgo_step(void* h, const double* action, const double* u, const double* draw
 }
 int urgo_get_state(void* h, double* out) { Batch* b = (Batch*)h; for (size_t i = 0; i < b->envs.size(); i++) b->envs[i].get_state(out + STATE_SLOTS * i); return 0; }
 int urgo_set_state(void* h, const double* in) { Batch* b = (Batch*)h; for (size_t i = 0; i < b->envs.size(); i++) b->envs[i].set_state(in + STATE_SLOTS * i); return 0; }
+// pairs[N][EXPORT_MAXC][2] (-1 padded), count[N] = the true number of manifold points (may exceed EXPORT_MAXC)
 int urgo_contacts(void* h, int32_t* pairs, int32_t* count) {
   Batch* b = (Batch*)h;
   for (size_t i = 0; i < b->envs.size(); i++) {
-    const Env& e = b->envs[i]; count[i] = e.last_ncontacts;
-    for (int k = 0; k < MAXC; k++) { pairs[(i * MAXC + k) * 2] = k < e.last_ncontacts ? e.last_contacts[k][0] : -1; pairs[(i * MAXC + k) * 2 + 1] = k < e.last_ncontacts ? e.last_contacts[k][1] : -1; }
+    const Env& e = b->envs[i]; const int n = (int)e.last_contacts.size(); count[i] = n;
+    for (int k = 0; k < EXPORT_MAXC; k++) { pairs[(i * EXPORT_MAXC + k) * 2] = k < n ? e.last_contacts[k].first : -1; pairs[(i * EXPORT_MAXC + k) * 2 + 1] = k < n ? e.last_contacts[k].second : -1; }
   }
   return 0;
 }
+int urgo_export_maxc(void) { return EXPORT_MAXC; }
 // ---- env-logic entry points (no physics): the two halves of step() around wait_until_stable, and the command trace
 // out[16] = reward so far, motor targets[7], arm_armed, grip_armed
 int urgo_prologue(void* h, int env, const double* action, double u, double* out) {
@@ -421,7 +431,7 @@ int urgo_epilogue(void* h, int env, double reward_so_far, int npairs, const int3
                   uint8_t* truncated, uint8_t* success) {
   Env& e = ((Batch*)h)->envs[env];
   e.w.contacts.clear();
-  for (int i = 0; i < npairs && i < MAXC; i++) { Contact c; c.sa = pairs[2 * i]; c.sb = pairs[2 * i + 1]; e.w.contacts.push_back(c); }
+  for (int i = 0; i < npairs; i++) { Contact c; c.sa = pairs[2 * i]; c.sb = pairs[2 * i + 1]; e.w.contacts.push_back(c); }
   e.epilogue(reward_so_far, obs, reward, terminated, truncated, success);
   return 0;
 }
@@ -475,8 +485,8 @@ long urgo_total_ticks(void* h) { long s = 0; for (auto& e : ((Batch*)h)->envs) s
 // ---- unit-level entry points for parity tests
 // n ticks of raw physics on every env (no env logic); detail outputs of the last tick are optional
 int urgo_tick(void* h, int nticks) { for (auto& e : ((Batch*)h)->envs) for (int k = 0; k < nticks; k++) e.w.tick(); return 0; }
-int urgo_last_contacts_detail(void* h, int env, double* out /*[MAXC][11]: sa, sb, posB3, n3, dist, mu, roll*/) {
-  Env& e = ((Batch*)h)->envs[env]; int n = (int)e.w.contacts.size();
+int urgo_last_contacts_detail(void* h, int env, double* out /*[EXPORT_MAXC][11]: sa, sb, posB3, n3, dist, mu, roll*/) {
+  Env& e = ((Batch*)h)->envs[env]; int n = std::min((int)e.w.contacts.size(), (int)EXPORT_MAXC);
   for (int i = 0; i < n; i++) {
     const Contact& c = e.w.contacts[i]; double* o = out + 11 * i;
     o[0] = c.sa; o[1] = c.sb; o[2] = c.posB.x; o[3] = c.posB.y; o[4] = c.posB.z; o[5] = c.n.x; o[6] = c.n.y; o[7] = c.n.z; o[8] = c.dist; o[9] = c.mu; o[10] = c.roll;
@@ -488,12 +498,38 @@ void urgo_tick_stats(void* h, long* out5) {
   for (int k = 0; k < 5; k++) out5[k] = 0;
   for (auto& e : ((Batch*)h)->envs) { out5[0] += e.w.st_ticks; out5[1] += e.w.st_iters; out5[2] += e.w.st_rows; out5[3] += e.w.st_contacts; out5[4] += e.w.st_rowiters; }
 }
-void urgo_tick_hist(void* h, long* rows96, long* nc24, long* nnc32) {
-  for (int k = 0; k < 96; k++) rows96[k] = 0;
-  for (int k = 0; k < 24; k++) nc24[k] = 0;
+// histograms over ticks: solver rows [192], manifold points [64], joint rows [32], rolling-friction manifolds [16]
+void urgo_tick_hist(void* h, long* rows192, long* nc64, long* nnc32, long* roll16) {
+  for (int k = 0; k < 192; k++) rows192[k] = 0;
+  for (int k = 0; k < 64; k++) nc64[k] = 0;
   for (int k = 0; k < 32; k++) nnc32[k] = 0;
-  for (auto& e : ((Batch*)h)->envs) { for (int k = 0; k < 96; k++) rows96[k] += e.w.st_hist_rows[k]; for (int k = 0; k < 24; k++) nc24[k] += e.w.st_hist_nc[k]; for (int k = 0; k < 32; k++) nnc32[k] += e.w.st_hist_nnc[k]; }
+  for (int k = 0; k < 16; k++) roll16[k] = 0;
+  for (auto& e : ((Batch*)h)->envs) {
+    for (int k = 0; k < 192; k++) rows192[k] += e.w.st_hist_rows[k];
+    for (int k = 0; k < 64; k++) nc64[k] += e.w.st_hist_nc[k];
+    for (int k = 0; k < 32; k++) nnc32[k] += e.w.st_hist_nnc[k];
+    for (int k = 0; k < 16; k++) roll16[k] += e.w.st_hist_roll[k];
+  }
 }
+// run-time copy of a recalled parameter (bullet_params.h: BulletParams); affects worlds created afterwards. Returns 0 or -1.
+int urgo_set_param(const char* name, double v) {
+  BulletParams& P = bp(); std::string n(name);
+#define URGO_P(f) if (n == #f) { P.f = v; return 0; }
+  URGO_P(erp) URGO_P(erp2) URGO_P(linear_slop) URGO_P(restitution_threshold) URGO_P(lin_damping) URGO_P(ang_damping) URGO_P(contact_breaking)
+  URGO_P(motor_kp) URGO_P(motor_kd) URGO_P(ik_damping) URGO_P(max_friction) URGO_P(solver_iters) URGO_P(robot_mu) URGO_P(body_mu) URGO_P(cube_mu)
+  URGO_P(plane_mu) URGO_P(cube_mass) URGO_P(friction_cone) URGO_P(roll_points) URGO_P(link_mask) URGO_P(box_shrink)
+#undef URGO_P
+  return -1;
+}
+void urgo_reset_params(void) { bp() = BulletParams(); }
+// summed joint motion of each tick of the env's last wait_until_stable (out[max]); returns the tick count
+int urgo_settle_trace(void* h, int env, double* out, int max) {
+  Env& e = ((Batch*)h)->envs[env]; int n = (int)e.settle_l1.size();
+  for (int i = 0; i < n && i < max; i++) out[i] = e.settle_l1[i];
+  return n;
+}
+// how close the last tick's contact set came to being another one (see decision_margin in urgo_collide.h)
+double urgo_contact_margin(void* h, int env) { return ((Batch*)h)->envs[env].w.contact_margin; }
 int urgo_last_iters(void* h, int env) { return ((Batch*)h)->envs[env].w.last_iters; }
 // link frames for joint vector q[12]: out[19][7] = pos xyz, quat xyzw (getLinkState(...)[4], [5])
 void urgo_fk(const double* q, double* out) {

@@ -7,7 +7,7 @@ import numpy as np
 
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 ENV_TYPES = {'BallBalance': 0, 'TwoBallsBalance': 1, 'CubesPush': 2, 'CubesGrasp': 3, 'Golf': 4, 'CubesPushDiff': 5, 'GolfJoints': 6}
-MAXC = 16
+MAXC = 64          # width of the oracle's contact-pair export (urgo_export_maxc); the oracle itself keeps every point
 STATE_SLOTS = 96
 _lib = None
 
@@ -93,7 +93,8 @@ class OracleBatch:
 
     def contacts(self):
         pairs = np.zeros((self.n, MAXC, 2), np.int32); cnt = np.zeros(self.n, np.int32)
-        self.L.urgo_contacts(self.h, _p(pairs), _p(cnt)); return pairs, cnt
+        assert self.L.urgo_export_maxc() == MAXC
+        self.L.urgo_contacts(self.h, _p(pairs), _p(cnt)); return pairs, np.minimum(cnt, MAXC)
 
     def tick(self, n=1):
         self.L.urgo_tick(self.h, n)
@@ -101,11 +102,26 @@ class OracleBatch:
     def contacts_detail(self, env=0):
         out = np.zeros((MAXC, 11)); n = self.L.urgo_last_contacts_detail(self.h, env, _p(out)); return out[:n]
 
+    def settle_trace(self, env=0):
+        """Summed |joint motion| of every tick of the env's last wait_until_stable."""
+        out = np.zeros(480); n = self.L.urgo_settle_trace(self.h, env, _p(out), 480); return out[:n]
+
+    def contact_margin(self, env=0):
+        """Smallest |inequality slack| the narrowphase decided on in the env's last tick (how close the contact set came to another)."""
+        self.L.urgo_contact_margin.restype = C.c_double
+        return float(self.L.urgo_contact_margin(self.h, env))
+
     def last_iters(self, env=0):
         return self.L.urgo_last_iters(self.h, env)
 
     def set_sparse(self, flag):
         self.L.urgo_set_sparse(self.h, int(flag))
+
+    def tick_hist(self):
+        """Histograms over all ticks so far: solver rows, manifold points, joint rows, rolling-friction manifolds per tick."""
+        r, c, j, t = np.zeros(192, np.int64), np.zeros(64, np.int64), np.zeros(32, np.int64), np.zeros(16, np.int64)
+        self.L.urgo_tick_hist(self.h, _p(r), _p(c), _p(j), _p(t))
+        return dict(rows=r, contacts=c, joint_rows=j, rolling=t)
 
     def total_ticks(self):
         return self.L.urgo_total_ticks(self.h)
@@ -139,6 +155,17 @@ class OracleBatch:
         for i in range(self.L.urgo_num_shapes(self.t)):
             b, l = C.c_int(), C.c_int(); self.L.urgo_shape_info(self.t, i, C.byref(b), C.byref(l)); out.append((b.value, l.value))
         return out
+
+
+def set_param(name, value):
+    """Run-time copy of a recalled Bullet parameter (oracle/bullet_params.h: BulletParams); worlds created afterwards see it."""
+    L = lib(); L.urgo_set_param.argtypes = [C.c_char_p, C.c_double]
+    if L.urgo_set_param(name.encode(), float(value)) != 0:
+        raise KeyError(name)
+
+
+def reset_params():
+    lib().urgo_reset_params()
 
 
 def fk(q):

@@ -55,8 +55,9 @@ def test_static_queries_work_without_a_device(L):
         assert (L.urgym_obs_dim(t), L.urgym_act_dim(t), L.urgym_max_episode_steps(t)) == (od, ad, ms)
         g, sm = C.c_int(), C.c_int()
         assert L.urgym_kernel_info(t, C.byref(g), C.byref(sm)) == 0
-        assert g.value in (16, 32) and 0 < sm.value <= 24 * 1024
+        assert g.value == 32 and 0 < sm.value <= (18, 18, 32, 32, 56, 32, 56)[t] * 1024   # 13 / 7 / 4 resident envs per SM
     assert L.urgym_obs_dim(7) < 0
+    assert L.urgym_real_bytes() == 4 and [L.urgym_num_pairs(t) for t in range(7)] == [73, 94, 73, 35, 134, 73, 134]
 
 
 def test_shape_tables_agree_with_the_oracle(L):
@@ -91,6 +92,15 @@ def test_bad_arguments_are_rejected(L):
     assert L.urgym_create(9, 4, 0, 0, 0, 0, C.byref(C.c_void_p())) != 0
     assert L.urgym_create(0, 0, 0, 0, 0, 0, C.byref(C.c_void_p())) != 0
     assert L.urgym_step(None, *([None] * 10), 0, None) != 0
+
+
+def test_parity_build_exports_the_same_entry_points():
+    """liburgym_b200_f64.so = the same sources with real = double: same symbols, 8-byte scalars."""
+    from urgym_b200 import _lib
+    L64 = _lib.lib('f64')
+    for name in declared_functions():
+        assert hasattr(L64, name), name
+    assert L64.urgym_real_bytes() == 8 and L64.urgym_obs_dim(3) == 17
 
 
 def test_product_never_touches_the_oracle():

@@ -1,67 +1,36 @@
 #!/usr/bin/env python
-"""Replay the reference's shipped SB3 actors (trained on pybullet) on the CPU oracle and compare task statistics.
+"""Replay the reference's shipped SB3 actors (trained on pybullet) and compare task statistics with the checkpoints'.
 
-The checkpoints under /root/reference/policies_final/*/SAC_policy.zip hold actor weights (MLP obs -> 256 -> 256 ->
-act, ReLU, tanh-squashed mean) and, in their `data` JSON, the Monitor buffers of the last 100 training episodes on
-pybullet (return, length, success). If the oracle's physics behaves like Bullet's, a policy trained there must also
-solve the task here. This is the only end-to-end pin of the rigid-body arithmetic available without pybullet
-(SURVEY.md §8c "weak pins" 3). Nothing from the checkpoints is copied into the repo; run where /root/reference exists:
+The actors (tests/golden/actors.npz) are MLPs trained against pybullet; tests/golden/actors.json holds the Monitor
+statistics of their last 100 training episodes there. If the physics behaves like Bullet's, a policy trained there must
+also solve the task here: the only end-to-end pin of the rigid-body arithmetic available without pybullet.
 
-    python tools/replay_actors.py [--episodes 200] [--out profiles/r01_actor_replay.json]
+    python tools/replay_actors.py [--episodes 1000] [--backend oracle|cuda] [--set name=value ...] [--out file.json] [env ...]
+
+--backend oracle: the fp64 CPU restatement, all host threads (--set overrides recalled parameters, oracle/bullet_params.h).
+--backend cuda:   the CUDA library; the MLP runs in torch on the device and drives URGymVectorEnv-style stepping with no
+                  host synchronisation inside an episode.
 """
 import argparse
-import io
 import json
 import os
 import sys
-import zipfile
 from concurrent.futures import ThreadPoolExecutor
 
 import numpy as np
-import torch
 
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
 sys.path.insert(0, os.path.join(ROOT, 'tests'))
-import oracle_lib as O  # noqa: E402
+import actors as A  # noqa: E402
 
-REF = os.environ.get('URGYM_REFERENCE', '/root/reference')
-CASES = {'CubesPush': 'policies_final/cubes_push_v0/SAC_policy.zip', 'Golf': 'policies_final/golf_v0/SAC_policy.zip',
-         'GolfJoints': 'policies_final/golf_joints_v0/SAC_policy.zip'}
+ENVS = ['TwoBallsBalance', 'CubesPush', 'Golf', 'GolfJoints']
 
 
-def load_actor(path):
-    z = zipfile.ZipFile(path)
-    sd = torch.load(io.BytesIO(z.read('policy.pth')), map_location='cpu', weights_only=True)
-    data = json.loads(z.read('data'))
-    g = lambda k: sd[k].double().numpy()
-    W0, b0, W1, b1 = g('actor.latent_pi.0.weight'), g('actor.latent_pi.0.bias'), g('actor.latent_pi.2.weight'), g('actor.latent_pi.2.bias')
-    sde = 'actor.mu.0.weight' in sd          # gSDE actors: mu = Linear + Hardtanh(-2, 2)
-    Wm, bm = (g('actor.mu.0.weight'), g('actor.mu.0.bias')) if sde else (g('actor.mu.weight'), g('actor.mu.bias'))
-
-    def act(obs):  # deterministic SAC action, rescaled to the env's [-0.1, 0.1] box
-        x = np.asarray(obs, np.float32).astype(np.float64)
-        h = np.maximum(x @ W0.T + b0, 0); h = np.maximum(h @ W1.T + b1, 0)
-        m = h @ Wm.T + bm
-        if sde:
-            m = np.clip(m, -2.0, 2.0)
-        return 0.1 * np.tanh(m)
-    hist = dict(ep_info=data.get('ep_info_buffer'), ep_success=data.get('ep_success_buffer'), num_timesteps=data.get('num_timesteps'))
-    return act, hist
-
-
-def decode_buffer(b):
-    """SB3 serialises deques through cloudpickle+base64; the readable part we need is absent, so unpickle."""
-    import base64
-    import pickle
-    if not b or ':serialized:' not in b:
-        return None
-    try:
-        return list(pickle.loads(base64.b64decode(b[':serialized:'])))
-    except Exception as e:  # cloudpickle-only payloads
-        return None
-
-
-def rollout(name, act, episodes, seed, threads):
+def rollout_oracle(name, episodes, seed=123, threads=None):
+    import oracle_lib as O
+    act = A.numpy_actor(name)
+    threads = threads or min(32, os.cpu_count() or 1)
     n = episodes
     ob = O.OracleBatch(name, n, seed=seed)
     cuts = np.linspace(0, n, threads + 1).astype(int)
@@ -84,25 +53,61 @@ def rollout(name, act, episodes, seed, threads):
                 alive[sl] &= ~done
             if not alive.any():
                 break
-    return dict(episodes=n, mean_return=float(ret.mean()), mean_length=float(length.mean()), success_rate=float(succ.mean()))
+    return summarize(ret, length, succ)
+
+
+def rollout_cuda(name, episodes, seed=123, precision='f32'):
+    """First episode of `episodes` envs; everything stays on the device until the final statistics."""
+    import torch
+    from urgym_b200.batch import EnvBatch
+    dev = torch.device('cuda', 0)
+    act = A.torch_actor(name, dev)
+    b = EnvBatch(name, episodes, seed=seed, precision=precision)
+    obs = b.reset().clone()
+    alive = torch.ones(episodes, dtype=torch.bool, device=dev)
+    ret = torch.zeros(episodes, dtype=torch.float64, device=dev); length = torch.zeros(episodes, dtype=torch.int64, device=dev)
+    succ = torch.zeros(episodes, dtype=torch.bool, device=dev)
+    for k in range(b.max_episode_steps):
+        a = act(obs)
+        o, r, term, trunc, su = b.step(a, autoreset=False)
+        obs = torch.where(alive[:, None], o, obs)
+        ret += torch.where(alive, r.double(), torch.zeros_like(ret)); length += alive
+        succ |= su.bool() & alive
+        alive &= ~(term.bool() | trunc.bool())
+    out = summarize(ret.cpu().numpy(), length.cpu().numpy(), succ.cpu().numpy())
+    out['capacity_overflow_ticks'] = b.stats()['capacity_overflow_ticks']
+    b.close()
+    return out
+
+
+def summarize(ret, length, succ):
+    n = len(ret)
+    return dict(episodes=int(n), mean_return=float(ret.mean()), mean_length=float(length.mean()), success_rate=float(succ.mean()),
+                se_return=float(ret.std() / np.sqrt(n)), se_length=float(length.std() / np.sqrt(n)), se_success=float(succ.std() / np.sqrt(n)))
 
 
 def main():
     ap = argparse.ArgumentParser()
-    ap.add_argument('--episodes', type=int, default=200)
+    ap.add_argument('--episodes', type=int, default=1000)
+    ap.add_argument('--backend', default='oracle', choices=['oracle', 'cuda', 'cuda64'])
+    ap.add_argument('--set', action='append', default=[], help='oracle parameter override name=value (bullet_params.h: BulletParams)')
     ap.add_argument('--out', default='')
+    ap.add_argument('names', nargs='*')
     args = ap.parse_args()
-    O.build()
+    if args.backend == 'oracle':
+        import oracle_lib as O
+        O.build()
+        for kv in args.set:
+            k, v = kv.split('=')
+            O.set_param(k, float(v))
     results = {}
-    for name, rel in CASES.items():
-        act, hist = load_actor(os.path.join(REF, rel))
-        info, suc = decode_buffer(hist['ep_info']), decode_buffer(hist['ep_success'])
-        trained = None
-        if info:
-            trained = dict(episodes=len(info), mean_return=float(np.mean([e['r'] for e in info])), mean_length=float(np.mean([e['l'] for e in info])),
-                           success_rate=float(np.mean(suc)) if suc else None)
-        r = rollout(name, act, args.episodes, seed=123, threads=min(16, os.cpu_count() or 1))
-        results[name] = dict(oracle_replay=r, pybullet_training_last_100=trained, checkpoint=rel, num_timesteps=hist['num_timesteps'])
+    for name in (args.names or ENVS):
+        if args.backend == 'oracle':
+            r = rollout_oracle(name, args.episodes)
+        else:
+            r = rollout_cuda(name, args.episodes, precision='f64' if args.backend == 'cuda64' else 'f32')
+        results[name] = dict(replay=r, backend=args.backend, overrides=args.set, pybullet_training_last_100=A.META[name]['pybullet_training_last_100'],
+                             checkpoint=A.META[name]['checkpoint'])
         print(name, json.dumps(results[name]), flush=True)
     if args.out:
         with open(args.out, 'w') as f:

@@ -8,27 +8,31 @@ import os
 
 HERE = os.path.dirname(os.path.abspath(__file__))
 SO_PATH = os.environ.get('URGYM_SO') or os.path.join(HERE, 'liburgym_b200.so')   # URGYM_SO: A/B builds of the same ABI
+# the parity build: same sources and entry points with urgym_real = double (include/urgym_b200.h, urgym_b200/build.py)
+SO_PATH_F64 = os.environ.get('URGYM_SO_F64') or os.path.join(HERE, 'liburgym_b200_f64.so')
 
 ENV_TYPES = {'BallBalance': 0, 'TwoBallsBalance': 1, 'CubesPush': 2, 'CubesGrasp': 3, 'Golf': 4, 'CubesPushDiff': 5, 'GolfJoints': 6}
 STATE_FLOATS = 96
-MAX_CONTACTS = 16
+MAX_CONTACTS = 32      # width of the manifold-point export (include/urgym_b200.h: URGYM_MAX_CONTACTS)
+PAIR_WORDS = 5         # uint32 words of the per-pair contact mask (URGYM_PAIR_WORDS)
 NUM_LINKS = 19
 
-_lib = None
+_libs = {}
 
 
 class UrgymError(RuntimeError):
     pass
 
 
-def lib():
-    global _lib
-    if _lib is not None:
-        return _lib
-    if not os.path.exists(SO_PATH):
-        raise UrgymError('liburgym_b200.so is not built (run `python -m urgym_b200.build` or __graft_entry__.build()); '
-                         'urgym_b200 has no CPU path')
-    L = C.CDLL(SO_PATH)
+def lib(precision='f32'):
+    """The product library (precision 'f32') or the fp64 parity build ('f64')."""
+    if precision in _libs:
+        return _libs[precision]
+    path = {'f32': SO_PATH, 'f64': SO_PATH_F64}[precision]
+    if not os.path.exists(path):
+        raise UrgymError('%s is not built (run `python -m urgym_b200.build` or __graft_entry__.build()); '
+                         'urgym_b200 has no CPU path' % os.path.basename(path))
+    L = C.CDLL(path)
     vp, i32, u64 = C.c_void_p, C.c_int, C.c_uint64
     L.urgym_create.argtypes = [i32, i32, i32, u64, i32, i32, C.POINTER(vp)]
     L.urgym_destroy.argtypes = [vp]
@@ -39,6 +43,8 @@ def lib():
     L.urgym_get_state.argtypes = [vp, vp, vp]
     L.urgym_set_state.argtypes = [vp, vp, vp]
     L.urgym_contacts.argtypes = [vp, vp, vp, vp]
+    L.urgym_contact_pairs.argtypes = [vp, vp, vp]
+    L.urgym_pair_info.argtypes = [i32, i32, C.POINTER(i32), C.POINTER(i32)]
     L.urgym_tick.argtypes = [vp, i32, vp]
     L.urgym_step_logic.argtypes = [vp] + [vp] * 10
     L.urgym_fk.argtypes = [i32, i32, vp, vp, vp]
@@ -49,13 +55,16 @@ def lib():
     L.urgym_kernel_info.argtypes = [i32, C.POINTER(i32), C.POINTER(i32)]
     L.urgym_launch_count.restype = C.c_longlong
     L.urgym_last_error.restype = C.c_char_p
-    _lib = L
+    if L.urgym_real_bytes() != {'f32': 4, 'f64': 8}[precision]:
+        raise UrgymError('%s was built for another scalar width than %s' % (path, precision))
+    L.precision = precision
+    _libs[precision] = L
     return L
 
 
-def check(rc):
+def check(rc, L=None):
     if rc != 0:
-        raise UrgymError('urgym_b200 error %d: %s' % (rc, lib().urgym_last_error().decode()))
+        raise UrgymError('urgym_b200 error %d: %s' % (rc, (L or lib()).urgym_last_error().decode()))
 
 
 def shape_table(env_type):
@@ -66,4 +75,15 @@ def shape_table(env_type):
         b, l = C.c_int(), C.c_int()
         check(L.urgym_shape_info(env_type, i, C.byref(b), C.byref(l)))
         out.append((b.value, l.value))
+    return out
+
+
+def pair_table(env_type, precision='f32'):
+    """[(shape_a, shape_b)] of the scene's candidate pairs, in the bit order of urgym_contact_pairs."""
+    L = lib(precision)
+    out = []
+    for i in range(L.urgym_num_pairs(env_type)):
+        a, b = C.c_int(), C.c_int()
+        check(L.urgym_pair_info(env_type, i, C.byref(a), C.byref(b)), L)
+        out.append((a.value, b.value))
     return out

@@ -7,6 +7,9 @@
 #include <string>
 #include <vector>
 
+#if defined(UG_F64) && !defined(URGYM_F64)
+#define URGYM_F64 1
+#endif
 #include "../../include/urgym_b200.h"
 #ifndef UG_DEFAULT_GROUP
 #define UG_DEFAULT_GROUP 32
@@ -33,9 +36,9 @@ struct urgym_env_s {
   int env_type, N, device, gidx0, sparse;
   uint64_t seed;
   DevModel hmodel; DevModel* dmodel = nullptr;
-  float* state = nullptr; int32_t* contacts = nullptr; int32_t* ccount = nullptr; double* stats = nullptr;
+  real* state = nullptr; int32_t* contacts = nullptr; int32_t* ccount = nullptr; uint32_t* hitmask = nullptr; double* stats = nullptr;
   // staging for the *_host entry points
-  float *d_action = nullptr, *d_u = nullptr, *d_draws = nullptr, *d_obs = nullptr, *d_final = nullptr, *d_reward = nullptr;
+  real *d_action = nullptr, *d_u = nullptr, *d_draws = nullptr, *d_obs = nullptr, *d_final = nullptr, *d_reward = nullptr;
   uint8_t *d_term = nullptr, *d_trunc = nullptr, *d_succ = nullptr, *d_mask = nullptr; int32_t* d_nticks = nullptr;
   uint8_t* d_defer = nullptr; bool split_reset = false;  // auto-reset in its own launch
   cudaStream_t own_stream = nullptr, last_stream = nullptr;
@@ -43,13 +46,9 @@ struct urgym_env_s {
 
 namespace {
 
-// G lanes of a warp run one env: a whole warp by default, URGYM_GROUP=16 packs two envs into a warp
-// (kept for comparison runs).
-int group_size() {
-  static int g = 0;
-  if (!g) { const char* e = getenv("URGYM_GROUP"); g = (e && atoi(e) == 32) ? 32 : (e && atoi(e) == 16 ? 16 : UG_DEFAULT_GROUP); }
-  return g;
-}
+// One warp runs one env. Two envs per warp (16-lane groups) was measured in round 1 and lost on every
+// scene; with up to 32 manifold points per tick the normal rows need the 32 lanes anyway.
+int group_size() { return 32; }
 
 // Whether auto-resets run in a launch of their own. Measured per env type (profiles/r01_reset_scheduling.txt): the
 // ball scenes gain 7-19% because step ticks and the robot-only ticks of a reset no longer share an SM, the scenes whose
@@ -64,7 +63,7 @@ template <int ENV, int G>
 int launch_env_g(urgym_handle h, const KParams& P, cudaStream_t st) {
   static bool attr_done[16] = {false};
   constexpr int EPB = 32 / G;  // envs per 32-thread block
-  size_t smem = sizeof(SmemT<EnvRC<ENV>::value>) * EPB;
+  size_t smem = sizeof(EnvSmem<ENV>) * EPB;
   if (getenv("URGYM_EXTRA_SMEM")) smem += (size_t)atoi(getenv("URGYM_EXTRA_SMEM"));  // occupancy experiments only
   if (!attr_done[h->device & 15]) {
     CK(cudaFuncSetAttribute(env_kernel<ENV, G>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
@@ -79,12 +78,12 @@ int launch_env_g(urgym_handle h, const KParams& P, cudaStream_t st) {
 }
 template <int ENV>
 int launch_env(urgym_handle h, const KParams& P, cudaStream_t st) {
-  return group_size() == 32 ? launch_env_g<ENV, 32>(h, P, st) : launch_env_g<ENV, 16>(h, P, st);
+  return launch_env_g<ENV, 32>(h, P, st);
 }
 
 int launch(urgym_handle h, KParams& P, void* stream) {
   CK(cudaSetDevice(h->device));
-  P.model = h->dmodel; P.state = h->state; P.N = h->N; P.contacts = h->contacts; P.ccount = h->ccount; P.stats = h->stats;
+  P.model = h->dmodel; P.state = h->state; P.N = h->N; P.contacts = h->contacts; P.ccount = h->ccount; P.hitmask = h->hitmask; P.stats = h->stats;
   P.seed = h->seed; P.gidx0 = h->gidx0; P.sparse = h->sparse;
   cudaStream_t st = (cudaStream_t)stream;  // NULL = the legacy default stream, as in the CUDA runtime
   switch (h->env_type) {
@@ -140,22 +139,24 @@ int urgym_create(int env_type, int num_envs, int device, uint64_t seed, int env_
   size_t n = (size_t)num_envs; int od = h->hmodel.obs_dim, ad = h->hmodel.act_dim;
   CK(cudaMalloc(&h->dmodel, sizeof(DevModel)));
   CK(cudaMemcpy(h->dmodel, &h->hmodel, sizeof(DevModel), cudaMemcpyHostToDevice));
-  CK(cudaMalloc(&h->state, n * UG_STATE * sizeof(float)));
+  CK(cudaMalloc(&h->state, n * UG_STATE * sizeof(real)));
   CK(cudaMalloc(&h->contacts, n * UG_MAXC * 2 * sizeof(int32_t)));
   CK(cudaMalloc(&h->ccount, n * sizeof(int32_t)));
+  CK(cudaMalloc(&h->hitmask, n * UG_HITWORDS * sizeof(uint32_t)));
+  CK(cudaMemset(h->hitmask, 0, n * UG_HITWORDS * sizeof(uint32_t)));
   CK(cudaMalloc(&h->stats, 8 * sizeof(double)));
   CK(cudaMemset(h->stats, 0, 8 * sizeof(double)));
   CK(cudaMemset(h->contacts, 0xff, n * UG_MAXC * 2 * sizeof(int32_t)));
   CK(cudaMemset(h->ccount, 0, n * sizeof(int32_t)));
-  CK(cudaMalloc(&h->d_action, n * ad * sizeof(float))); CK(cudaMalloc(&h->d_u, n * sizeof(float))); CK(cudaMalloc(&h->d_draws, n * 4 * sizeof(float)));
-  CK(cudaMalloc(&h->d_obs, n * od * sizeof(float))); CK(cudaMalloc(&h->d_final, n * od * sizeof(float))); CK(cudaMalloc(&h->d_reward, n * sizeof(float)));
+  CK(cudaMalloc(&h->d_action, n * ad * sizeof(real))); CK(cudaMalloc(&h->d_u, n * sizeof(real))); CK(cudaMalloc(&h->d_draws, n * 4 * sizeof(real)));
+  CK(cudaMalloc(&h->d_obs, n * od * sizeof(real))); CK(cudaMalloc(&h->d_final, n * od * sizeof(real))); CK(cudaMalloc(&h->d_reward, n * sizeof(real)));
   CK(cudaMalloc(&h->d_term, n)); CK(cudaMalloc(&h->d_trunc, n)); CK(cudaMalloc(&h->d_succ, n)); CK(cudaMalloc(&h->d_mask, n));
   CK(cudaMalloc(&h->d_nticks, n * 2 * sizeof(int32_t)));
   CK(cudaMalloc(&h->d_defer, n)); CK(cudaMemset(h->d_defer, 0, n));
   CK(cudaStreamCreateWithFlags(&h->own_stream, cudaStreamNonBlocking));
-  std::vector<float> init(n * UG_STATE, 0.f);
-  for (size_t i = 0; i < n; i++) { float* r = init.data() + i * UG_STATE; r[37] = 1.f; for (int b = 0; b < UG_MAXFREE; b++) r[38 + 13 * b + 6] = 1.f; }
-  CK(cudaMemcpy(h->state, init.data(), init.size() * sizeof(float), cudaMemcpyHostToDevice));
+  std::vector<real> init(n * UG_STATE, 0._r);
+  for (size_t i = 0; i < n; i++) { real* r = init.data() + i * UG_STATE; r[37] = 1._r; for (int b = 0; b < UG_MAXFREE; b++) r[38 + 13 * b + 6] = 1._r; }
+  CK(cudaMemcpy(h->state, init.data(), init.size() * sizeof(real), cudaMemcpyHostToDevice));
   *out = h;
   return URGYM_OK;
 }
@@ -164,22 +165,22 @@ int urgym_destroy(urgym_handle h) {
   if (!h) return URGYM_OK;
   cudaSetDevice(h->device);
   cudaDeviceSynchronize();
-  void* ptrs[] = {h->dmodel, h->state, h->contacts, h->ccount, h->stats, h->d_action, h->d_u, h->d_draws, h->d_obs, h->d_final, h->d_reward, h->d_term, h->d_trunc, h->d_succ, h->d_mask, h->d_nticks, h->d_defer};
+  void* ptrs[] = {h->dmodel, h->state, h->contacts, h->ccount, h->hitmask, h->stats, h->d_action, h->d_u, h->d_draws, h->d_obs, h->d_final, h->d_reward, h->d_term, h->d_trunc, h->d_succ, h->d_mask, h->d_nticks, h->d_defer};
   for (void* p : ptrs) if (p) cudaFree(p);
   if (h->own_stream) cudaStreamDestroy(h->own_stream);
   delete h;
   return URGYM_OK;
 }
 
-int urgym_reset(urgym_handle h, const uint8_t* mask_dev, const float* draws_dev, float* obs_dev, int32_t* nticks_dev, void* stream) {
+int urgym_reset(urgym_handle h, const uint8_t* mask_dev, const real* draws_dev, real* obs_dev, int32_t* nticks_dev, void* stream) {
   if (!h || !obs_dev) return fail(URGYM_E_ARG, "urgym_reset: null argument");
   KParams P; std::memset(&P, 0, sizeof(P));
   P.mode = MODE_RESET; P.mask = mask_dev; P.draws = draws_dev; P.obs = obs_dev; P.nticks = nticks_dev;
   return launch(h, P, stream);
 }
 
-int urgym_step(urgym_handle h, const float* action_dev, const float* u_dev, const float* draws_dev, float* obs_dev, float* reward_dev,
-               uint8_t* terminated_dev, uint8_t* truncated_dev, uint8_t* success_dev, float* final_obs_dev, int32_t* nticks_dev,
+int urgym_step(urgym_handle h, const real* action_dev, const real* u_dev, const real* draws_dev, real* obs_dev, real* reward_dev,
+               uint8_t* terminated_dev, uint8_t* truncated_dev, uint8_t* success_dev, real* final_obs_dev, int32_t* nticks_dev,
                int autoreset, void* stream) {
   if (!h || !action_dev || !obs_dev || !reward_dev || !terminated_dev || !truncated_dev || !success_dev) return fail(URGYM_E_ARG, "urgym_step: null argument");
   KParams P; std::memset(&P, 0, sizeof(P));
@@ -195,8 +196,8 @@ int urgym_step(urgym_handle h, const float* action_dev, const float* u_dev, cons
   return launch(h, R, stream);
 }
 
-int urgym_step_logic(urgym_handle h, const float* action_dev, const float* u_dev, const int32_t* pairs_dev, const int32_t* count_dev,
-                     float* obs_dev, float* reward_dev, uint8_t* terminated_dev, uint8_t* truncated_dev, uint8_t* success_dev, void* stream) {
+int urgym_step_logic(urgym_handle h, const real* action_dev, const real* u_dev, const int32_t* pairs_dev, const int32_t* count_dev,
+                     real* obs_dev, real* reward_dev, uint8_t* terminated_dev, uint8_t* truncated_dev, uint8_t* success_dev, void* stream) {
   if (!h || !action_dev || !pairs_dev || !count_dev || !obs_dev || !reward_dev || !terminated_dev || !truncated_dev || !success_dev)
     return fail(URGYM_E_ARG, "urgym_step_logic: null argument");
   KParams P; std::memset(&P, 0, sizeof(P));
@@ -212,55 +213,55 @@ int urgym_tick(urgym_handle h, int nticks, void* stream) {
   return launch(h, P, stream);
 }
 
-int urgym_step_host(urgym_handle h, const float* action, const float* u, const float* draws, float* obs, float* reward, uint8_t* terminated,
-                    uint8_t* truncated, uint8_t* success, float* final_obs, int32_t* nticks, int autoreset) {
+int urgym_step_host(urgym_handle h, const real* action, const real* u, const real* draws, real* obs, real* reward, uint8_t* terminated,
+                    uint8_t* truncated, uint8_t* success, real* final_obs, int32_t* nticks, int autoreset) {
   if (!h || !action || !obs || !reward || !terminated || !truncated || !success) return fail(URGYM_E_ARG, "urgym_step_host: null argument");
   CK(cudaSetDevice(h->device));
   size_t n = (size_t)h->N; int od = h->hmodel.obs_dim, ad = h->hmodel.act_dim; cudaStream_t st = h->own_stream;
-  CK(cudaMemcpyAsync(h->d_action, action, n * ad * sizeof(float), cudaMemcpyHostToDevice, st));
-  if (u) CK(cudaMemcpyAsync(h->d_u, u, n * sizeof(float), cudaMemcpyHostToDevice, st));
-  if (draws) CK(cudaMemcpyAsync(h->d_draws, draws, n * 4 * sizeof(float), cudaMemcpyHostToDevice, st));
+  CK(cudaMemcpyAsync(h->d_action, action, n * ad * sizeof(real), cudaMemcpyHostToDevice, st));
+  if (u) CK(cudaMemcpyAsync(h->d_u, u, n * sizeof(real), cudaMemcpyHostToDevice, st));
+  if (draws) CK(cudaMemcpyAsync(h->d_draws, draws, n * 4 * sizeof(real), cudaMemcpyHostToDevice, st));
   int rc = urgym_step(h, h->d_action, u ? h->d_u : nullptr, draws ? h->d_draws : nullptr, h->d_obs, h->d_reward, h->d_term, h->d_trunc, h->d_succ,
                       h->d_final, h->d_nticks, autoreset, st);
   if (rc) return rc;
-  CK(cudaMemcpyAsync(obs, h->d_obs, n * od * sizeof(float), cudaMemcpyDeviceToHost, st));
-  CK(cudaMemcpyAsync(reward, h->d_reward, n * sizeof(float), cudaMemcpyDeviceToHost, st));
+  CK(cudaMemcpyAsync(obs, h->d_obs, n * od * sizeof(real), cudaMemcpyDeviceToHost, st));
+  CK(cudaMemcpyAsync(reward, h->d_reward, n * sizeof(real), cudaMemcpyDeviceToHost, st));
   CK(cudaMemcpyAsync(terminated, h->d_term, n, cudaMemcpyDeviceToHost, st));
   CK(cudaMemcpyAsync(truncated, h->d_trunc, n, cudaMemcpyDeviceToHost, st));
   CK(cudaMemcpyAsync(success, h->d_succ, n, cudaMemcpyDeviceToHost, st));
-  if (final_obs) CK(cudaMemcpyAsync(final_obs, h->d_final, n * od * sizeof(float), cudaMemcpyDeviceToHost, st));
+  if (final_obs) CK(cudaMemcpyAsync(final_obs, h->d_final, n * od * sizeof(real), cudaMemcpyDeviceToHost, st));
   if (nticks) CK(cudaMemcpyAsync(nticks, h->d_nticks, n * 2 * sizeof(int32_t), cudaMemcpyDeviceToHost, st));
   CK(cudaStreamSynchronize(st));
   return URGYM_OK;
 }
 
-int urgym_reset_host(urgym_handle h, const uint8_t* mask, const float* draws, float* obs, int32_t* nticks) {
+int urgym_reset_host(urgym_handle h, const uint8_t* mask, const real* draws, real* obs, int32_t* nticks) {
   if (!h || !obs) return fail(URGYM_E_ARG, "urgym_reset_host: null argument");
   CK(cudaSetDevice(h->device));
   size_t n = (size_t)h->N; int od = h->hmodel.obs_dim; cudaStream_t st = h->own_stream;
   if (mask) CK(cudaMemcpyAsync(h->d_mask, mask, n, cudaMemcpyHostToDevice, st));
-  if (draws) CK(cudaMemcpyAsync(h->d_draws, draws, n * 4 * sizeof(float), cudaMemcpyHostToDevice, st));
-  if (mask) CK(cudaMemcpyAsync(h->d_obs, obs, n * od * sizeof(float), cudaMemcpyHostToDevice, st));  // unmasked rows keep the caller's values
+  if (draws) CK(cudaMemcpyAsync(h->d_draws, draws, n * 4 * sizeof(real), cudaMemcpyHostToDevice, st));
+  if (mask) CK(cudaMemcpyAsync(h->d_obs, obs, n * od * sizeof(real), cudaMemcpyHostToDevice, st));  // unmasked rows keep the caller's values
   int rc = urgym_reset(h, mask ? h->d_mask : nullptr, draws ? h->d_draws : nullptr, h->d_obs, h->d_nticks, st);
   if (rc) return rc;
-  CK(cudaMemcpyAsync(obs, h->d_obs, n * od * sizeof(float), cudaMemcpyDeviceToHost, st));
+  CK(cudaMemcpyAsync(obs, h->d_obs, n * od * sizeof(real), cudaMemcpyDeviceToHost, st));
   if (nticks) CK(cudaMemcpyAsync(nticks, h->d_nticks, n * sizeof(int32_t), cudaMemcpyDeviceToHost, st));
   CK(cudaStreamSynchronize(st));
   return URGYM_OK;
 }
 
-int urgym_get_state(urgym_handle h, float* state_dev, void* stream) {
+int urgym_get_state(urgym_handle h, real* state_dev, void* stream) {
   if (!h || !state_dev) return fail(URGYM_E_ARG, "urgym_get_state: null argument");
   CK(cudaSetDevice(h->device));
   cudaStream_t st = (cudaStream_t)stream;  // NULL = the legacy default stream, as in the CUDA runtime
-  CK(cudaMemcpyAsync(state_dev, h->state, (size_t)h->N * UG_STATE * sizeof(float), cudaMemcpyDeviceToDevice, st));
+  CK(cudaMemcpyAsync(state_dev, h->state, (size_t)h->N * UG_STATE * sizeof(real), cudaMemcpyDeviceToDevice, st));
   h->last_stream = st; return URGYM_OK;
 }
-int urgym_set_state(urgym_handle h, const float* state_dev, void* stream) {
+int urgym_set_state(urgym_handle h, const real* state_dev, void* stream) {
   if (!h || !state_dev) return fail(URGYM_E_ARG, "urgym_set_state: null argument");
   CK(cudaSetDevice(h->device));
   cudaStream_t st = (cudaStream_t)stream;  // NULL = the legacy default stream, as in the CUDA runtime
-  CK(cudaMemcpyAsync(h->state, state_dev, (size_t)h->N * UG_STATE * sizeof(float), cudaMemcpyDeviceToDevice, st));
+  CK(cudaMemcpyAsync(h->state, state_dev, (size_t)h->N * UG_STATE * sizeof(real), cudaMemcpyDeviceToDevice, st));
   h->last_stream = st; return URGYM_OK;
 }
 int urgym_contacts(urgym_handle h, int32_t* pairs_dev, int32_t* count_dev, void* stream) {
@@ -272,19 +273,32 @@ int urgym_contacts(urgym_handle h, int32_t* pairs_dev, int32_t* count_dev, void*
   h->last_stream = st; return URGYM_OK;
 }
 
-int urgym_fk(int device, int n, const float* q_dev, float* pose_dev, void* stream) {
+int urgym_contact_pairs(urgym_handle h, uint32_t* mask_dev, void* stream) {
+  if (!h || !mask_dev) return fail(URGYM_E_ARG, "urgym_contact_pairs: null argument");
+  CK(cudaSetDevice(h->device));
+  cudaStream_t st = (cudaStream_t)stream;
+  CK(cudaMemcpyAsync(mask_dev, h->hitmask, (size_t)h->N * UG_HITWORDS * sizeof(uint32_t), cudaMemcpyDeviceToDevice, st));
+  h->last_stream = st; return URGYM_OK;
+}
+int urgym_num_pairs(int t) { DevModel m; return build_model(t, &m) ? URGYM_E_ARG : m.npairs; }
+int urgym_pair_info(int t, int pair, int* shape_a, int* shape_b) {
+  DevModel m; if (build_model(t, &m) || pair < 0 || pair >= m.npairs || !shape_a || !shape_b) return fail(URGYM_E_ARG, "bad pair index");
+  *shape_a = m.pairs[pair][0]; *shape_b = m.pairs[pair][1]; return URGYM_OK;
+}
+
+int urgym_fk(int device, int n, const real* q_dev, real* pose_dev, void* stream) {
   if (n <= 0 || !q_dev || !pose_dev) return fail(URGYM_E_ARG, "urgym_fk: bad arguments");
   DevModel* dm; int rc = kin_model(device, &dm); if (rc) return rc;
   fk_kernel<<<(n + 63) / 64, 64, 0, (cudaStream_t)stream>>>(dm, n, q_dev, pose_dev); g_launches++;
   CK(cudaGetLastError()); return URGYM_OK;
 }
-int urgym_ik(int device, int n, const float* q_dev, const float* target_dev, float* out_dev, void* stream) {
+int urgym_ik(int device, int n, const real* q_dev, const real* target_dev, real* out_dev, void* stream) {
   if (n <= 0 || !q_dev || !target_dev || !out_dev) return fail(URGYM_E_ARG, "urgym_ik: bad arguments");
   DevModel* dm; int rc = kin_model(device, &dm); if (rc) return rc;
   ik_kernel<<<(n + 63) / 64, 64, 0, (cudaStream_t)stream>>>(dm, n, q_dev, target_dev, out_dev); g_launches++;
   CK(cudaGetLastError()); return URGYM_OK;
 }
-int urgym_gripper_center(int device, int n, const float* q_dev, float* out_dev, void* stream) {
+int urgym_gripper_center(int device, int n, const real* q_dev, real* out_dev, void* stream) {
   if (n <= 0 || !q_dev || !out_dev) return fail(URGYM_E_ARG, "urgym_gripper_center: bad arguments");
   DevModel* dm; int rc = kin_model(device, &dm); if (rc) return rc;
   CK(cudaFuncSetAttribute(gripper_center_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(SmemKin)));
@@ -292,17 +306,19 @@ int urgym_gripper_center(int device, int n, const float* q_dev, float* out_dev, 
   CK(cudaGetLastError()); return URGYM_OK;
 }
 
-int urgym_stats(urgym_handle h, double out[6]) {
+int urgym_stats(urgym_handle h, double out[8]) {
   if (!h || !out) return fail(URGYM_E_ARG, "urgym_stats: null argument");
   CK(cudaSetDevice(h->device));
   if (h->last_stream) CK(cudaStreamSynchronize(h->last_stream));
-  CK(cudaMemcpy(out, h->stats, 6 * sizeof(double), cudaMemcpyDeviceToHost));
+  CK(cudaMemcpy(out, h->stats, 8 * sizeof(double), cudaMemcpyDeviceToHost));
   return URGYM_OK;
 }
 int urgym_kernel_info(int env_type, int* group_lanes, int* smem_bytes_per_env) {
   if (env_type < 0 || env_type >= UG_ENV_COUNT || !group_lanes || !smem_bytes_per_env) return fail(URGYM_E_ARG, "urgym_kernel_info: bad arguments");
   *group_lanes = group_size();
-  *smem_bytes_per_env = (env_type == 4 || env_type == 6) ? (int)sizeof(SmemT<EnvRC<4>::value>) : (int)sizeof(SmemT<EnvRC<0>::value>);
+  const int sz[UG_ENV_COUNT] = {(int)sizeof(EnvSmem<0>), (int)sizeof(EnvSmem<1>), (int)sizeof(EnvSmem<2>), (int)sizeof(EnvSmem<3>), (int)sizeof(EnvSmem<4>),
+                                (int)sizeof(EnvSmem<5>), (int)sizeof(EnvSmem<6>)};
+  *smem_bytes_per_env = sz[env_type];
   return URGYM_OK;
 }
 // Development aid (only meaningful in a -DUG_PHASE_TIMING build): summed per-phase warp cycles since the last call.
@@ -319,6 +335,7 @@ int urgym_phase_cycles(unsigned long long out[8]) {
 #endif
 }
 long long urgym_launch_count(void) { return g_launches.load(); }
+int urgym_real_bytes(void) { return (int)sizeof(real); }
 const char* urgym_last_error(void) { return g_err.c_str(); }
 
 }  // extern "C"

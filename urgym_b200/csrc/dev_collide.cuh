@@ -5,59 +5,59 @@
 #include "dev_math.cuh"
 
 struct BoxW { f3 c; m3 R; f3 h; };
-struct CPt { f3 posA, posB, n; float dist; };  // n from B to A
+struct CPt { f3 posA, posB, n; real dist; };  // n from B to A
 
-UG_DEV float edge_bias(float s) { return s < 0.f ? s * 1.05f : s / 1.05f; }
+UG_DEV real edge_bias(real s) { return s < 0._r ? s * 1.05_r : s / 1.05_r; }
 
 // Sutherland-Hodgman clip of a convex polygon (x,y,z per vertex) against |x|<=hx, |y|<=hy. Buffers hold 16 vertices.
-__device__ __noinline__ int clip_rect(float (*bufA)[3], int n, float hx, float hy, float (*bufB)[3], int* which) {
-  float (*src)[3] = bufA; float (*dst)[3] = bufB;
+__device__ __noinline__ int clip_rect(real (*bufA)[3], int n, real hx, real hy, real (*bufB)[3], int* which) {
+  real (*src)[3] = bufA; real (*dst)[3] = bufB;
   int flip = 0;
   for (int e = 0; e < 4; e++) {
-    int ax = e >> 1; float sgn = (e & 1) ? -1.0f : 1.0f; float lim = ax == 0 ? hx : hy;
+    int ax = e >> 1; real sgn = (e & 1) ? -1.0_r : 1.0_r; real lim = ax == 0 ? hx : hy;
     int m = 0;
     for (int i = 0; i < n; i++) {
-      const float* P = src[i]; const float* Q = src[(i + 1 == n) ? 0 : i + 1];
-      float dp = lim - sgn * P[ax], dq = lim - sgn * Q[ax];
-      if (dp >= 0.f) { dst[m][0] = P[0]; dst[m][1] = P[1]; dst[m][2] = P[2]; m++; }
-      if ((dp >= 0.f) != (dq >= 0.f)) {
-        float t = dp / (dp - dq);
+      const real* P = src[i]; const real* Q = src[(i + 1 == n) ? 0 : i + 1];
+      real dp = lim - sgn * P[ax], dq = lim - sgn * Q[ax];
+      if (dp >= 0._r) { dst[m][0] = P[0]; dst[m][1] = P[1]; dst[m][2] = P[2]; m++; }
+      if ((dp >= 0._r) != (dq >= 0._r)) {
+        real t = dp / (dp - dq);
         dst[m][0] = P[0] + t * (Q[0] - P[0]); dst[m][1] = P[1] + t * (Q[1] - P[1]); dst[m][2] = P[2] + t * (Q[2] - P[2]);
         m++;
       }
     }
     n = m;
-    float (*tmp)[3] = src; src = dst; dst = tmp; flip ^= 1;
+    real (*tmp)[3] = src; src = dst; dst = tmp; flip ^= 1;
     if (n == 0) break;
   }
   *which = flip;  // 0: result in bufA, 1: result in bufB
   return n;
 }
 
-__device__ __noinline__ int box_box(const BoxW& A, const BoxW& B, float margin, CPt* out) {
+__device__ __noinline__ int box_box(const BoxW& A, const BoxW& B, real margin, CPt* out) {
   f3 p = B.c - A.c;
   f3 pp = tmulv(A.R, p);
-  float R[3][3], Q[3][3];
+  real R[3][3], Q[3][3];
 #pragma unroll
   for (int i = 0; i < 3; i++)
 #pragma unroll
-    for (int j = 0; j < 3; j++) { R[i][j] = dot(col(A.R, i), col(B.R, j)); Q[i][j] = fabsf(R[i][j]); }
-  float best = -1e30f; int code = 0; bool invert = false; f3 nrm = mk3(0, 0, 1);
+    for (int j = 0; j < 3; j++) { R[i][j] = dot(col(A.R, i), col(B.R, j)); Q[i][j] = rabs(R[i][j]); }
+  real best = -1e30_r; int code = 0; bool invert = false; f3 nrm = mk3(0, 0, 1);
 #pragma unroll
   for (int i = 0; i < 3; i++) {
-    float e1 = comp(pp, i);
-    float e2 = comp(A.h, i) + B.h.x * Q[i][0] + B.h.y * Q[i][1] + B.h.z * Q[i][2];
-    float s = fabsf(e1) - e2;
+    real e1 = comp(pp, i);
+    real e2 = comp(A.h, i) + B.h.x * Q[i][0] + B.h.y * Q[i][1] + B.h.z * Q[i][2];
+    real s = rabs(e1) - e2;
     if (s > margin) return 0;
-    if (s > best) { best = s; nrm = col(A.R, i); invert = e1 < 0.f; code = 1 + i; }
+    if (s > best) { best = s; nrm = col(A.R, i); invert = e1 < 0._r; code = 1 + i; }
   }
 #pragma unroll
   for (int j = 0; j < 3; j++) {
-    float e1 = dot(col(B.R, j), p);
-    float e2 = A.h.x * Q[0][j] + A.h.y * Q[1][j] + A.h.z * Q[2][j] + comp(B.h, j);
-    float s = fabsf(e1) - e2;
+    real e1 = dot(col(B.R, j), p);
+    real e2 = A.h.x * Q[0][j] + A.h.y * Q[1][j] + A.h.z * Q[2][j] + comp(B.h, j);
+    real s = rabs(e1) - e2;
     if (s > margin) return 0;
-    if (s > best) { best = s; nrm = col(B.R, j); invert = e1 < 0.f; code = 4 + j; }
+    if (s > best) { best = s; nrm = col(B.R, j); invert = e1 < 0._r; code = 4 + j; }
   }
 #pragma unroll
   for (int i = 0; i < 3; i++) {
@@ -67,28 +67,28 @@ __device__ __noinline__ int box_box(const BoxW& A, const BoxW& B, float margin, 
       const int j1 = (j + 1) % 3, j2 = (j + 2) % 3;
       f3 L = mk3(0, 0, 0);
       setc(L, i1, -R[i2][j]); setc(L, i2, R[i1][j]);
-      float l = norm3(L);
-      if (l <= 1e-9f) continue;
-      float e1 = dot(pp, L);
-      float e2 = comp(A.h, i1) * Q[i2][j] + comp(A.h, i2) * Q[i1][j] + comp(B.h, j1) * Q[i][j2] + comp(B.h, j2) * Q[i][j1];
-      float s = (fabsf(e1) - e2) / l;
+      real l = norm3(L);
+      if (l <= 1e-9_r) continue;
+      real e1 = dot(pp, L);
+      real e2 = comp(A.h, i1) * Q[i2][j] + comp(A.h, i2) * Q[i1][j] + comp(B.h, j1) * Q[i][j2] + comp(B.h, j2) * Q[i][j1];
+      real s = (rabs(e1) - e2) / l;
       if (s > margin) return 0;
-      if (edge_bias(s) > best) { best = s; nrm = mulv(A.R, L * (1.0f / l)); invert = e1 < 0.f; code = 7 + 3 * i + j; }
+      if (edge_bias(s) > best) { best = s; nrm = mulv(A.R, L * (1.0_r / l)); invert = e1 < 0._r; code = 7 + 3 * i + j; }
     }
   }
   if (invert) nrm = -nrm;
-  float depth = -best;
+  real depth = -best;
   if (code >= 7) {
     int i = (code - 7) / 3, j = (code - 7) % 3;
     f3 pa = A.c, pb = B.c;
 #pragma unroll
     for (int k = 0; k < 3; k++) {
-      pa = pa + col(A.R, k) * ((dot(nrm, col(A.R, k)) > 0.f ? 1.0f : -1.0f) * comp(A.h, k));
-      pb = pb - col(B.R, k) * ((dot(nrm, col(B.R, k)) > 0.f ? 1.0f : -1.0f) * comp(B.h, k));
+      pa = pa + col(A.R, k) * ((dot(nrm, col(A.R, k)) > 0._r ? 1.0_r : -1.0_r) * comp(A.h, k));
+      pb = pb - col(B.R, k) * ((dot(nrm, col(B.R, k)) > 0._r ? 1.0_r : -1.0_r) * comp(B.h, k));
     }
     f3 ua = col(A.R, i), ub = col(B.R, j), d = pb - pa;
-    float uaub = dot(ua, ub), q1 = dot(ua, d), q2 = -dot(ub, d), den = 1.0f - uaub * uaub, beta = 0.f;
-    if (den > 1e-4f) beta = (uaub * q1 + q2) / den;
+    real uaub = dot(ua, ub), q1 = dot(ua, d), q2 = -dot(ub, d), den = 1.0_r - uaub * uaub, beta = 0._r;
+    if (den > 1e-4_r) beta = (uaub * q1 + q2) / den;
     pb = pb + ub * beta;
     out[0].n = -nrm; out[0].dist = -depth; out[0].posB = pb; out[0].posA = pb + out[0].n * out[0].dist;
     return 1;
@@ -97,15 +97,15 @@ __device__ __noinline__ int box_box(const BoxW& A, const BoxW& B, float margin, 
   const BoxW& inc = code <= 3 ? B : A;
   f3 nr = code <= 3 ? nrm : -nrm;
   int k = (code - 1) % 3, c1 = (k + 1) % 3, c2 = (k + 2) % 3;
-  int la = 0; float lav = -1.f;
+  int la = 0; real lav = -1._r;
 #pragma unroll
-  for (int j = 0; j < 3; j++) { float v = fabsf(dot(nr, col(inc.R, j))); if (v > lav) { lav = v; la = j; } }
+  for (int j = 0; j < 3; j++) { real v = rabs(dot(nr, col(inc.R, j))); if (v > lav) { lav = v; la = j; } }
   int a1 = (la + 1) % 3, a2 = (la + 2) % 3;
-  float sg = dot(nr, col(inc.R, la)) > 0.f ? -1.0f : 1.0f;
+  real sg = dot(nr, col(inc.R, la)) > 0._r ? -1.0_r : 1.0_r;
   f3 fc = inc.c + col(inc.R, la) * (sg * comp(inc.h, la)) - ref.c;
   f3 e1v = col(inc.R, a1) * comp(inc.h, a1), e2v = col(inc.R, a2) * comp(inc.h, a2);
   f3 rc1 = col(ref.R, c1), rc2 = col(ref.R, c2);
-  float bufA[16][3], bufB[16][3];
+  real bufA[16][3], bufB[16][3];
   {
     f3 quad[4] = {fc - e1v - e2v, fc + e1v - e2v, fc + e1v + e2v, fc - e1v + e2v};
 #pragma unroll
@@ -113,18 +113,18 @@ __device__ __noinline__ int box_box(const BoxW& A, const BoxW& B, float margin, 
   }
   int which;
   int n = clip_rect(bufA, 4, comp(ref.h, c1), comp(ref.h, c2), bufB, &which);
-  float (*cl)[3] = which ? bufB : bufA;
-  int keep[16]; float dep[16]; int m = 0;
-  float hk = comp(ref.h, k);
-  for (int v = 0; v < n; v++) { float dv = hk - cl[v][2]; if (dv >= -margin) { keep[m] = v; dep[m] = dv; m++; } }
+  real (*cl)[3] = which ? bufB : bufA;
+  int keep[16]; real dep[16]; int m = 0;
+  real hk = comp(ref.h, k);
+  for (int v = 0; v < n; v++) { real dv = hk - cl[v][2]; if (dv >= -margin) { keep[m] = v; dep[m] = dv; m++; } }
   if (m == 0) return 0;
   int cnt = m < 4 ? m : 4, i0 = 0;
   if (m > 4) for (int v = 1; v < m; v++) if (dep[v] > dep[i0]) i0 = v;
   for (int j = 0; j < cnt; j++) {
     int s = m > 4 ? (i0 + (j * m) / 4) % m : j;
-    const float* c = cl[keep[s]];
+    const real* c = cl[keep[s]];
     f3 pt = ref.c + rc1 * c[0] + rc2 * c[1] + nr * c[2];
-    float dv = dep[s];
+    real dv = dep[s];
     out[j].n = -nrm; out[j].dist = -dv;
     if (code <= 3) { out[j].posB = pt; out[j].posA = pt + out[j].n * out[j].dist; }
     else { out[j].posA = pt; out[j].posB = pt - out[j].n * out[j].dist; }
@@ -132,18 +132,18 @@ __device__ __noinline__ int box_box(const BoxW& A, const BoxW& B, float margin, 
   return cnt;
 }
 
-UG_DEV bool sphere_box(f3 sc, float r, const BoxW& B, float margin, f3& on_box, f3& n_bs, float& dist) {
+UG_DEV bool sphere_box(f3 sc, real r, const BoxW& B, real margin, f3& on_box, f3& n_bs, real& dist) {
   f3 l = tmulv(B.R, sc - B.c);
-  f3 cl = mk3(fminf(fmaxf(l.x, -B.h.x), B.h.x), fminf(fmaxf(l.y, -B.h.y), B.h.y), fminf(fmaxf(l.z, -B.h.z), B.h.z));
+  f3 cl = mk3(rmin(rmax(l.x, -B.h.x), B.h.x), rmin(rmax(l.y, -B.h.y), B.h.y), rmin(rmax(l.z, -B.h.z), B.h.z));
   f3 d = l - cl;
-  float len2 = dot(d, d);
+  real len2 = dot(d, d);
   f3 nl;
-  if (len2 > 1e-24f) { float len = sqrtf(len2); nl = d * (1.0f / len); dist = len - r; }
+  if (len2 > 1e-24_r) { real len = rsqrt_(len2); nl = d * (1.0_r / len); dist = len - r; }
   else {
-    int ax = 0; float md = B.h.x - fabsf(l.x);
-    float v1 = B.h.y - fabsf(l.y); if (v1 < md) { md = v1; ax = 1; }
-    float v2 = B.h.z - fabsf(l.z); if (v2 < md) { md = v2; ax = 2; }
-    nl = mk3(0, 0, 0); float sgn = comp(l, ax) >= 0.f ? 1.0f : -1.0f; setc(nl, ax, sgn);
+    int ax = 0; real md = B.h.x - rabs(l.x);
+    real v1 = B.h.y - rabs(l.y); if (v1 < md) { md = v1; ax = 1; }
+    real v2 = B.h.z - rabs(l.z); if (v2 < md) { md = v2; ax = 2; }
+    nl = mk3(0, 0, 0); real sgn = comp(l, ax) >= 0._r ? 1.0_r : -1.0_r; setc(nl, ax, sgn);
     cl = l; setc(cl, ax, sgn * comp(B.h, ax));
     dist = -md - r;
   }

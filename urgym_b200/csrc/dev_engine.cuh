@@ -20,37 +20,39 @@
 struct Con {
   int shapes;   // sa | sb << 8
   int bodies;   // (fa + 1) | (fb + 1) << 8 | (ra + 1) << 16
-  float pa[3], rb[3], n[3];
-  float dist, mu, rest, roll;
+  real pa[3], rb[3], n[3];
+  real dist, mu, rest, roll;
 };
 
-template <int RC>
+template <int NCAP, int RC>
 struct SmemT {
+  static constexpr int NC_CAP = NCAP;  // manifold points kept per tick
   static constexpr int TSQ = RC * RC + 32;  // + slack: lanes without a row still issue the (unused) operand load
   // ---- state that lives across the ticks of one gym step
-  float q[UG_NDOF], qd[UG_NDOF], tgt[8];
-  float fpos[UG_MAXFREE][3], fquat[UG_MAXFREE][4], flin[UG_MAXFREE][3], fang[UG_MAXFREE][3];
-  int flags, ncon, pad0, pad1;
+  real q[UG_NDOF], qd[UG_NDOF], tgt[8];
+  real fpos[UG_MAXFREE][3], fquat[UG_MAXFREE][4], flin[UG_MAXFREE][3], fang[UG_MAXFREE][3];
+  int flags, ncon, ovf, pad1;   // ovf: ticks of this launch whose manifold points / rolling manifolds exceeded the capacity
+  unsigned hit[UG_HITWORDS];     // pairs of the scene's pair list with at least one manifold point this tick (set before the cap)
   // ---- per tick
-  float vstar[32];
-  float bR[UG_NDOF][9], bp[UG_NDOF][3], ax[UG_NDOF][3];
-  float fR[UG_MAXFREE][9], fIinv[UG_MAXFREE][6];
-  Con con[UG_MAXC];
-  float lam[UG_JMAX + RC];
+  real vstar[32];
+  real bR[UG_NDOF][9], bp[UG_NDOF][3], ax[UG_NDOF][3];
+  real fR[UG_MAXFREE][9], fIinv[UG_MAXFREE][6];
+  Con con[NCAP];
+  real lam[UG_JMAX + RC];
   int jdesc[UG_JMAX];  // col | type << 8 | index << 12
   int jci4[UG_JMAX + 2];  // byte offset of row j's column inside an E row, at [j + 1] (one slack entry on each side)
   int cdesc[RC];       // contact | type << 8 | dir << 12
   // rows 0..16: extended M^-1 (17 x 17); rows 17..: robot velocity response of each contact row in the same 17 columns
-  float E[(UG_NCOL + RC) * UG_NCOL];
+  real E[(UG_NCOL + RC) * UG_NCOL];
   union alignas(16) {
-    float T[TSQ];  // contact-space Delassus block, full symmetric RC x RC: a step of row r reads row r, lane = own row
+    real T[TSQ];  // contact-space Delassus block, full symmetric RC x RC: a step of row r reads row r, lane = own row
     struct {
-      float M[UG_NDOF][UG_NDOF];  // mass matrix, then M^-1 (16-byte aligned rows for the row build)
-      float cm[UG_NDOF][3], Iw[UG_NDOF][6];
-      float w[UG_NDOF][3], vp[UG_NDOF][3], al[UG_NDOF][3], wr[UG_NDOF][6];
-      float tauv[16];
+      real M[UG_NDOF][UG_NDOF];  // mass matrix, then M^-1 (16-byte aligned rows for the row build)
+      real cm[UG_NDOF][3], Iw[UG_NDOF][6];
+      real w[UG_NDOF][3], vp[UG_NDOF][3], al[UG_NDOF][3], wr[UG_NDOF][6];
+      real tauv[16];
     } d;
-    float st[UG_STATE];
+    real st[UG_STATE];
   } u;
 };
 
@@ -64,7 +66,7 @@ struct SmemT {
 enum { RT_LIM_LO = 0, RT_LIM_HI = 1, RT_MOTOR = 2, RT_GEAR = 3, RT_NORMAL = 4, RT_ROLL = 5, RT_FRIC = 6, RT_PAD = 7 };
 
 __device__ __constant__ int c_gear_dof[5] = {7, 8, 9, 10, 11};
-__device__ __constant__ float c_gear_ratio[5] = {1.0f, -1.0f, -1.0f, 1.0f, -1.0f};
+__device__ __constant__ real c_gear_ratio[5] = {1.0_r, -1.0_r, -1.0_r, 1.0_r, -1.0_r};
 
 // ---------------------------------------------------------------------------------------------------------------
 // Forward kinematics of the 12 movable bodies, level by level (arm chain, then the four gripper branches).
@@ -81,7 +83,7 @@ UG_DEV void fk_bodies(S& s, const DevModel& M, const Gp<G>& gp) {
       else { Rp.m[0] = 1; Rp.m[1] = 0; Rp.m[2] = 0; Rp.m[3] = 0; Rp.m[4] = 1; Rp.m[5] = 0; Rp.m[6] = 0; Rp.m[7] = 0; Rp.m[8] = 1; pp = mk3(0, 0, 0); }
       m3 R0 = mulm(Rp, ldm(M.jrot[d]));
       f3 pos = pp + mulv(Rp, ld3(M.jpos[d]));
-      float sn, cs; __sincosf(s.q[d], &sn, &cs);  // |q| <= pi: the fast path is accurate to ~5e-7 there
+      real sn, cs; rsincos_fast(s.q[d], &sn, &cs);  // |q| <= pi: the fast path is accurate to ~5e-7 there
       int a = M.axis[d], j = (a + 1) % 3, k = (a + 2) % 3;
       f3 cj = col(R0, j), ck = col(R0, k);
       f3 nj = cj * cs + ck * sn, nk = ck * cs - cj * sn;
@@ -147,9 +149,9 @@ UG_DEV void dynamics(S& s, const DevModel& M, const Gp<G>& gp) {
   f3 f = (ac - mk3(0, 0, M.gravity)) * M.mass[d];
   f3 n;
   {
-    float Iwd[6]; rot_sym(Rd, M.I[d], Iwd);
+    real Iwd[6]; rot_sym(Rd, M.I[d], Iwd);
     n = symv(Iwd, al) + cross(w, symv(Iwd, w));
-    float wn = norm3(w);
+    real wn = norm3(w);
     f3 wl = tmulv(Rd, w);
 #pragma unroll 1
     for (int k = 0; k < M.nsub[d]; k++) {
@@ -161,22 +163,22 @@ UG_DEV void dynamics(S& s, const DevModel& M, const Gp<G>& gp) {
       f = f + fd; n = n + td + cross(cs - cmd, fd);
     }
   }
-  if (isd) { float* o = s.u.d.wr[d]; o[0] = n.x; o[1] = n.y; o[2] = n.z; o[3] = f.x; o[4] = f.y; o[5] = f.z; }
-  for (int i = l; i < UG_NDOF * UG_NDOF; i += G) (&s.u.d.M[0][0])[i] = 0.f;
+  if (isd) { real* o = s.u.d.wr[d]; o[0] = n.x; o[1] = n.y; o[2] = n.z; o[3] = f.x; o[4] = f.y; o[5] = f.z; }
+  for (int i = l; i < UG_NDOF * UG_NDOF; i += G) (&s.u.d.M[0][0])[i] = 0._r;
   gp.sync();
   // --- bias torque and mass-matrix row of dof d from composite sums over its subtree, about its own joint origin
-  float tau = 0.f;
+  real tau = 0._r;
   {
     const uint32_t sub = M.sub[d];
     f3 ad = ld3(s.ax[d]);
-    f3 h = mk3(0, 0, 0); float IO[6] = {0, 0, 0, 0, 0, 0};
+    f3 h = mk3(0, 0, 0); real IO[6] = {0, 0, 0, 0, 0, 0};
 #pragma unroll 1
     for (int b = 0; b < UG_NDOF; b++) if (sub >> b & 1) {
       f3 r = ld3(s.u.d.cm[b]) - pd;
-      const float* wb = s.u.d.wr[b]; const float* Ib = s.u.d.Iw[b];
+      const real* wb = s.u.d.wr[b]; const real* Ib = s.u.d.Iw[b];
       f3 nb = mk3(wb[0], wb[1], wb[2]), fb = mk3(wb[3], wb[4], wb[5]);
       tau += dot(ad, nb + cross(r, fb));
-      float mb = M.mass[b], rr = dot(r, r);
+      real mb = M.mass[b], rr = dot(r, r);
       h = h + r * mb;
       IO[0] += Ib[0] + mb * (rr - r.x * r.x); IO[1] += Ib[1] - mb * r.x * r.y; IO[2] += Ib[2] - mb * r.x * r.z;
       IO[3] += Ib[3] + mb * (rr - r.y * r.y); IO[4] += Ib[4] - mb * r.y * r.z; IO[5] += Ib[5] + mb * (rr - r.z * r.z);
@@ -186,7 +188,7 @@ UG_DEV void dynamics(S& s, const DevModel& M, const Gp<G>& gp) {
 #pragma unroll 1
     for (int j = 0; j < UG_NDOF; j++) if (anc >> j & 1) {
       f3 aj = ld3(s.ax[j]);
-      float v = dot(aj, nn) + dot(cross(aj, pd - ld3(s.bp[j])), ff);
+      real v = dot(aj, nn) + dot(cross(aj, pd - ld3(s.bp[j])), ff);
       s.u.d.M[d][j] = v; s.u.d.M[j][d] = v;
     }
   }
@@ -194,15 +196,15 @@ UG_DEV void dynamics(S& s, const DevModel& M, const Gp<G>& gp) {
   // --- Cholesky factor in shared memory (rolled: lane i produces row i of column k), then lane k solves for column k
   //     of M^-1 with the factor read back as broadcasts. Diagonal entries hold reciprocals.
   {
-    float (*A)[UG_NDOF] = s.u.d.M;
+    real (*A)[UG_NDOF] = s.u.d.M;
 #pragma unroll 1
     for (int k = 0; k < UG_NDOF; k++) {
-      float dk = A[k][k];
+      real dk = A[k][k];
 #pragma unroll 1
       for (int t = 0; t < k; t++) dk -= A[k][t] * A[k][t];
-      const float inv = rsqrtf(dk);
+      const real inv = rrsqrt(dk);
       if (l > k && l < UG_NDOF) {
-        float v = A[l][k];
+        real v = A[l][k];
 #pragma unroll 1
         for (int t = 0; t < k; t++) v -= A[l][t] * A[k][t];
         A[l][k] = v * inv;
@@ -211,17 +213,17 @@ UG_DEV void dynamics(S& s, const DevModel& M, const Gp<G>& gp) {
       if (l == k) A[k][k] = inv;
     }
     gp.sync();
-    float x[UG_NDOF];
+    real x[UG_NDOF];
 #pragma unroll
     for (int i = 0; i < UG_NDOF; i++) {
-      float v = (i == l) ? 1.0f : 0.0f;
+      real v = (i == l) ? 1.0_r : 0.0_r;
 #pragma unroll
       for (int t = 0; t < i; t++) v -= A[i][t] * x[t];
       x[i] = v * A[i][i];
     }
 #pragma unroll
     for (int i = UG_NDOF - 1; i >= 0; i--) {
-      float v = x[i];
+      real v = x[i];
 #pragma unroll
       for (int t = i + 1; t < UG_NDOF; t++) v -= A[t][i] * x[t];
       x[i] = v * A[i][i];
@@ -234,7 +236,7 @@ UG_DEV void dynamics(S& s, const DevModel& M, const Gp<G>& gp) {
 #pragma unroll
       for (int gi = 0; gi < 5; gi++) s.E[l * UG_NCOL + 12 + gi] = x[6] + c_gear_ratio[gi] * x[7 + gi];
     }
-    if (l < 16) s.u.d.tauv[l] = isd ? -tau : 0.f;
+    if (l < 16) s.u.d.tauv[l] = isd ? -tau : 0._r;
   }
   gp.sync();
   // gear rows 12..16 of the extended matrix: E[12+g][b] = E[6][b] + ratio_g * E[gear_dof_g][b]
@@ -243,10 +245,10 @@ UG_DEV void dynamics(S& s, const DevModel& M, const Gp<G>& gp) {
     for (int gi = 0; gi < 5; gi++) s.E[(12 + gi) * UG_NCOL + b] = s.E[6 * UG_NCOL + b] + c_gear_ratio[gi] * s.E[(7 + gi) * UG_NCOL + b];
   }
   if (isd) {
-    float qdd = 0.f;
+    real qdd = 0._r;
 #pragma unroll
     for (int j = 0; j < UG_NDOF; j++) qdd += s.u.d.M[d][j] * s.u.d.tauv[j];
-    s.vstar[d] = fminf(fmaxf(s.qd[d] + UGP_DT * qdd, -UGP_MAX_COORD_VEL), UGP_MAX_COORD_VEL);
+    s.vstar[d] = rmin(rmax(s.qd[d] + UGP_DT * qdd, -UGP_MAX_COORD_VEL), UGP_MAX_COORD_VEL);
   } else if (l < UG_NDOF + UG_MAXFREE) {
     int b = l - UG_NDOF;
     bool act = (s.flags & (FL_BODY0 << b)) != 0 && b < M.nfree;
@@ -260,13 +262,13 @@ UG_DEV void dynamics(S& s, const DevModel& M, const Gp<G>& gp) {
       f3 tq = -(Iwl * (UGP_ANG_DAMPING + UGP_ANG_DAMPING * norm3(wl))) - cross(wl, Iwl);
       f3 alf = mk3(tq.x / I.x, tq.y / I.y, tq.z / I.z);
       lin = lin + acc * UGP_DT; ang = ang + mulv(R, alf) * UGP_DT;
-      float inv[6] = {1.0f / I.x, 0.f, 0.f, 1.0f / I.y, 0.f, 1.0f / I.z};
+      real inv[6] = {1.0_r / I.x, 0._r, 0._r, 1.0_r / I.y, 0._r, 1.0_r / I.z};
       rot_sym(R, inv, s.fIinv[b]);
     } else {
       lin = mk3(0, 0, 0); ang = mk3(0, 0, 0);
-      for (int k = 0; k < 6; k++) s.fIinv[b][k] = 0.f;
+      for (int k = 0; k < 6; k++) s.fIinv[b][k] = 0._r;
     }
-    float* v = s.vstar + UG_NDOF + 6 * b;
+    real* v = s.vstar + UG_NDOF + 6 * b;
     v[0] = lin.x; v[1] = lin.y; v[2] = lin.z; v[3] = ang.x; v[4] = ang.y; v[5] = ang.z;
   }
   gp.sync();

@@ -38,16 +38,21 @@ UG_DEV f3 shape_center(const S& s, const DevShape& Sh) {
   return lc;
 }
 
-// Two passes. Pass 1, lane per candidate pair: bounding-sphere cull (sphere against the static boxes themselves),
-// survivors are compacted in pair order into a byte list in the (idle) solver scratch. Pass 2, lane per surviving pair:
-// narrowphase. Manifold points are appended in pair order and capped at UG_MAXC; the order is the
-// oracle's because the compaction keeps it. A tick with 113 candidate pairs (Golf) and 9 close ones costs one
-// narrowphase round instead of four.
+// Two passes. Pass 1, lane per candidate pair: bounding-sphere cull against the pair's bound M.cullr (sphere against the
+// static boxes themselves); survivors are compacted in pair order into a byte list in the (idle) solver scratch. The
+// bound is conservative for the narrowphase below: a culled pair could not have produced a manifold point
+// (model_build.cpp). Pass 2, lane per surviving pair: narrowphase. Manifold points are appended in pair order up to the
+// scene's capacity S::NC_CAP (the checker keeps them all; a tick that had more is counted in s.ovf and reported through
+// urgym_stats); the bit of every pair with at least one point is set in s.hit BEFORE the cap, so the contact predicates
+// and the pair export never depend on the capacity. A tick with 130 candidate pairs (Golf) and 9 close ones costs one
+// narrowphase round.
 template <int G, class S>
 __device__ __noinline__ void collide(S& s, const DevModel& M, const Gp<G> gp) {
+  constexpr int NCAP = S::NC_CAP;
   const int l = gp.l;
   unsigned char* near_list = reinterpret_cast<unsigned char*>(s.u.T);  // UG_MAXPAIRS bytes; T is dead between ticks
   int nnear = 0;
+  if (l < UG_HITWORDS) s.hit[l] = 0u;
 #pragma unroll 1
   for (int p0 = 0; p0 < M.npairs; p0 += G) {
     const int p = p0 + l;
@@ -57,14 +62,13 @@ __device__ __noinline__ void collide(S& s, const DevModel& M, const Gp<G> gp) {
       const bool actA = A.body <= 0 || (s.flags & (FL_BODY0 << (A.body - 1)));
       const bool actB = B.body <= 0 || (s.flags & (FL_BODY0 << (B.body - 1)));
       if (actA && actB) {
-        const float margin = fminf(A.cbt, B.cbt);
         const f3 ca = shape_center(s, A), cb = shape_center(s, B);
         const f3 dc = ca - cb;
         if (B.body < 0) {  // static boxes are axis-aligned in the world (table, plane, pitch)
           const f3 h = ld3(B.half);
-          const f3 e = mk3(fmaxf(fabsf(dc.x) - h.x, 0.f), fmaxf(fabsf(dc.y) - h.y, 0.f), fmaxf(fabsf(dc.z) - h.z, 0.f));
-          near = norm3(e) <= A.brad + margin;
-        } else near = norm3(dc) <= A.brad + B.brad + margin;
+          const f3 e = mk3(rmax(rabs(dc.x) - h.x, 0._r), rmax(rabs(dc.y) - h.y, 0._r), rmax(rabs(dc.z) - h.z, 0._r));
+          near = norm3(e) <= M.cullr[p];
+        } else near = norm3(dc) <= M.cullr[p];
       }
     }
     const unsigned m = gp.ballot(near);
@@ -74,27 +78,27 @@ __device__ __noinline__ void collide(S& s, const DevModel& M, const Gp<G> gp) {
   gp.sync();
   int base = 0;
 #pragma unroll 1
-  for (int i0 = 0; i0 < nnear && base < UG_MAXC; i0 += G) {
-    int n = 0, sa = 0, sb = 0;
+  for (int i0 = 0; i0 < nnear; i0 += G) {
+    int n = 0, sa = 0, sb = 0, p = 0;
     CPt pts[4];
     if (i0 + l < nnear) {
-      const int p = near_list[i0 + l];
+      p = near_list[i0 + l];
       sa = M.pairs[p][0]; sb = M.pairs[p][1];
       const DevShape& A = M.shapes[sa]; const DevShape& B = M.shapes[sb];
-      const float margin = fminf(A.cbt, B.cbt);
+      const real margin = rmin(A.cbt, B.cbt);
       BoxW a, b; shape_box(s, A, a); shape_box(s, B, b);
       const f3 dc = a.c - b.c;
       if (A.kind == 0 && B.kind == 0) n = box_box(a, b, margin, pts);
       else if (A.kind == 1 && B.kind == 0) {
-        f3 ob, nb; float d;
+        f3 ob, nb; real d;
         if (sphere_box(a.c, A.radius, b, margin, ob, nb, d)) { pts[0].n = nb; pts[0].dist = d; pts[0].posB = ob; pts[0].posA = ob + nb * d; n = 1; }
       } else if (A.kind == 0 && B.kind == 1) {
-        f3 oa, na; float d;
+        f3 oa, na; real d;
         if (sphere_box(b.c, B.radius, a, margin, oa, na, d)) { pts[0].n = -na; pts[0].dist = d; pts[0].posA = oa; pts[0].posB = oa + na * d; n = 1; }
       } else {
-        float len = norm3(dc), d = len - A.radius - B.radius;
+        real len = norm3(dc), d = len - A.radius - B.radius;
         if (d < margin) {
-          f3 nn = len > 1e-12f ? dc * (1.0f / len) : mk3(1, 0, 0);
+          f3 nn = len > 1e-12_r ? dc * (1.0_r / len) : mk3(1, 0, 0);
           pts[0].n = nn; pts[0].dist = d; pts[0].posB = b.c + nn * B.radius; pts[0].posA = pts[0].posB + nn * d; n = 1;
         }
       }
@@ -104,33 +108,34 @@ __device__ __noinline__ void collide(S& s, const DevModel& M, const Gp<G> gp) {
     for (int o = 1; o < G; o <<= 1) { int t = __shfl_up_sync(gp.mask, incl, o, G); if (l >= o) incl += t; }
     int excl = incl - n, total = gp.shfl(incl, G - 1);
     if (n > 0) {
+      atomicOr(&s.hit[p >> 5], 1u << (p & 31));
       const DevShape& A = M.shapes[sa]; const DevShape& B = M.shapes[sb];
-      float mu = fminf(fmaxf(A.mu * B.mu, -UGP_MAX_FRICTION), UGP_MAX_FRICTION);
-      float roll = fminf(fmaxf(A.roll * B.mu + B.roll * A.mu, -UGP_MAX_FRICTION), UGP_MAX_FRICTION);
+      real mu = rmin(rmax(A.mu * B.mu, -UGP_MAX_FRICTION), UGP_MAX_FRICTION);
+      real roll = rmin(rmax(A.roll * B.mu + B.roll * A.mu, -UGP_MAX_FRICTION), UGP_MAX_FRICTION);
       const int fa = A.body > 0 ? A.body - 1 : -1, fb = B.body > 0 ? B.body - 1 : -1, ra = A.body == 0 ? A.rbody : -1;
 #pragma unroll 1
       for (int i = 0; i < n; i++) {
         int idx = base + excl + i;
-        if (idx < UG_MAXC) {
+        if (idx < NCAP) {
           Con& c = s.con[idx];
           c.shapes = sa | (sb << 8); c.bodies = (fa + 1) | ((fb + 1) << 8) | ((ra + 1) << 16);
           st3(c.pa, fa >= 0 ? pts[i].posA - ld3(s.fpos[fa]) : pts[i].posA);
           st3(c.rb, fb >= 0 ? pts[i].posB - ld3(s.fpos[fb]) : pts[i].posB);
           st3(c.n, pts[i].n);
-          c.dist = pts[i].dist; c.mu = mu; c.rest = A.rest * B.rest; c.roll = i == 0 ? roll : 0.f;
+          c.dist = pts[i].dist; c.mu = mu; c.rest = A.rest * B.rest; c.roll = i == 0 ? roll : 0._r;
         }
       }
     }
-    base = min(base + total, UG_MAXC);
+    base += total;
   }
-  if (l == 0) s.ncon = base;
+  if (l == 0) { s.ncon = min(base, NCAP); if (base > NCAP) s.ovf++; }
   gp.sync();
 }
 
 // Jacobian of one contact-type row: 12 robot entries plus the linear / angular blocks of the (at most two) free
 // bodies it touches. Register-resident (static indexing only).
 struct CRow {
-  float Jr[UG_NDOF];
+  real Jr[UG_NDOF];
   f3 JlA, JaA, JlB, JaB;
   int fa, fb;
 };
@@ -154,7 +159,7 @@ UG_DEV void build_crow(const S& s, const DevModel& M, int desc, CRow& r, bool ro
     const uint32_t anc = ra >= 0 ? M.anc[ra] : 0u;
 #pragma unroll
     for (int d = 0; d < UG_NDOF; d++) {
-      float v = 0.f;
+      real v = 0._r;
       if (anc >> d & 1) {
         f3 a = ld3(s.ax[d]);
         v = lin ? dot(dv, cross(a, pa - ld3(s.bp[d]))) : dot(dv, a);
@@ -171,25 +176,25 @@ UG_DEV f3 pick3(const f3* a, int b) { return b == 0 ? a[0] : (b == 1 ? a[1] : a[
 // plus the owner's impulse update: no operand loads, no address arithmetic, no loop counter, no guards. The operations
 // and their order are those of the generic sweep (same bits). Returns the number of sweeps done; lam0 = the impulse.
 template <int N, class S>
-UG_DEV int joint_sweeps_reg(const S& s, const Gp<32>& gp, unsigned aE_own, float rhs0, float invd0, float lo0, float hi0, float den0, float& lam0) {
+UG_DEV int joint_sweeps_reg(const S& s, const Gp<32>& gp, unsigned aE_own, real rhs0, real invd0, real lo0, real hi0, real den0, real& lam0) {
   const int l = gp.l;
-  float e[N];
+  real e[N];
 #pragma unroll
   for (int r = 0; r < N; r++) e[r] = lds(aE_own + (unsigned)s.jci4[r + 1]);
-  float w0 = 0.f;
+  real w0 = 0._r;
   int it = 0;
 #define UG_JR_STEP(R)                                                                                    \
   {                                                                                                      \
-    float d_ = fmaf(-w0, invd0, rhs0);                                                                   \
-    d_ = fminf(fmaxf(d_, blo), bhi);                                                                     \
-    const float delta = gp.shfl(d_, (R));                                                                \
+    real d_ = rfma(-w0, invd0, rhs0);                                                                   \
+    d_ = rmin(rmax(d_, blo), bhi);                                                                     \
+    const real delta = gp.shfl(d_, (R));                                                                \
     if (l == (R)) lam0 += delta;                                                                         \
-    w0 = fmaf(e[(R)], delta, w0);                                                                        \
+    w0 = rfma(e[(R)], delta, w0);                                                                        \
   }
 #pragma unroll 1
   for (; it < UGP_SOLVER_ITERS;) {
     // a lane's impulse changes only at its own step, so its clamp bounds are constant over the sweep
-    const float blo = lo0 - lam0, bhi = hi0 - lam0, lamp0 = lam0;
+    const real blo = lo0 - lam0, bhi = hi0 - lam0, lamp0 = lam0;
     if (it & 1) {
 #pragma unroll
       for (int r = 0; r < N; r++) UG_JR_STEP(r)
@@ -198,7 +203,7 @@ UG_DEV int joint_sweeps_reg(const S& s, const Gp<32>& gp, unsigned aE_own, float
       for (int r = N - 1; r >= 0; r--) UG_JR_STEP(r)
     }
     it++;
-    const float r_ = (lam0 - lamp0) * den0;
+    const real r_ = (lam0 - lamp0) * den0;
     if (!gp.any(r_ * r_ > UGP_RESIDUAL_THRESHOLD)) break;
   }
 #undef UG_JR_STEP
@@ -209,7 +214,7 @@ UG_DEV int joint_sweeps_reg(const S& s, const Gp<32>& gp, unsigned aE_own, float
 // The sweep loops are kept rolled and small on purpose: one Gauss-Seidel sweep has to stay resident in the ~6 KB L0
 // instruction cache, because it runs 50 times per tick and is ~80 % of the kernel's time (profiles/).
 template <int G, int RC, class S>
-__device__ __noinline__ float solve_and_integrate(S& s, const DevModel& M, const Gp<G> gp, int* iters_out) {
+__device__ __noinline__ real solve_and_integrate(S& s, const DevModel& M, const Gp<G> gp, int* iters_out) {
   constexpr int NSJ = (UG_JMAX + G - 1) / G, NSC = (RC + G - 1) / G, NS = NSJ + NSC;
   const int l = gp.l;
   const int NC = s.ncon;
@@ -219,39 +224,41 @@ __device__ __noinline__ float solve_and_integrate(S& s, const DevModel& M, const
   {
     int lim = 0;
     if (l < UG_NDOF) {
-      if (!(s.q[l] - M.lower[l] > 0.f)) lim = 1;
-      else if (!(M.upper[l] - s.q[l] > 0.f)) lim = 2;
+      if (!(s.q[l] - M.lower[l] > 0._r)) lim = 1;
+      else if (!(M.upper[l] - s.q[l] > 0._r)) lim = 2;
     }
     unsigned lm = gp.ballot(lim != 0);
     int nl = __popc(lm);
-    if (lim) { const int p_ = __popc(lm & ((1u << l) - 1u)); s.jdesc[p_] = l | ((lim == 1 ? RT_LIM_LO : RT_LIM_HI) << 8) | (l << 12); s.jci4[p_ + 1] = 4 * l; }
+    if (lim) { const int p_ = __popc(lm & ((1u << l) - 1u)); s.jdesc[p_] = l | ((lim == 1 ? RT_LIM_LO : RT_LIM_HI) << 8) | (l << 12); s.jci4[p_ + 1] = (int)UG_RB * l; }
     int nm = 0;
     const int fl = s.flags;
-    if (fl & FL_ARM) { if (l < 6) { s.jdesc[nl + l] = l | (RT_MOTOR << 8) | (l << 12); s.jci4[nl + l + 1] = 4 * l; } nm = 6; }
-    if (fl & FL_GRIP) { if (l == 0) { s.jdesc[nl + nm] = 6 | (RT_MOTOR << 8) | (6 << 12); s.jci4[nl + nm + 1] = 4 * 6; } nm++; }
-    if (l < 5) { s.jdesc[nl + nm + l] = (12 + l) | (RT_GEAR << 8) | (l << 12); s.jci4[nl + nm + l + 1] = 4 * (12 + l); }
+    if (fl & FL_ARM) { if (l < 6) { s.jdesc[nl + l] = l | (RT_MOTOR << 8) | (l << 12); s.jci4[nl + l + 1] = (int)UG_RB * l; } nm = 6; }
+    if (fl & FL_GRIP) { if (l == 0) { s.jdesc[nl + nm] = 6 | (RT_MOTOR << 8) | (6 << 12); s.jci4[nl + nm + 1] = (int)UG_RB * 6; } nm++; }
+    if (l < 5) { s.jdesc[nl + nm + l] = (12 + l) | (RT_GEAR << 8) | (l << 12); s.jci4[nl + nm + l + 1] = (int)UG_RB * (12 + l); }
     n_nc = nl + nm + 5;
     if (l == 0) { s.jci4[0] = 0; s.jci4[n_nc + 1] = 0; }  // slack entries: the sweeps prefetch one row ahead
     if (l < NC) s.cdesc[l] = l | (RT_NORMAL << 8);
-    bool rl = l < NC && s.con[l].roll > 0.f;
+    bool rl = l < NC && s.con[l].roll > 0._r;
     unsigned rm = gp.ballot(rl);
-    NT = 2 * min(__popc(rm), UGP_MAX_ROLLING_CONTACTS);  // row capacity: RC = 16 + 32 + 2 * UGP_MAX_ROLLING_CONTACTS
+    constexpr int NROLL = (RC - 3 * S::NC_CAP) / 2;  // rolling-friction manifolds a tick can carry (Golf scenes: 4, else 0)
+    NT = 2 * min(__popc(rm), NROLL);
+    if (l == 0 && __popc(rm) > NROLL) s.ovf++;
     if (rl) {
       int r = __popc(rm & ((1u << l) - 1u));
-      if (r < UGP_MAX_ROLLING_CONTACTS) { s.cdesc[NC + 2 * r] = l | (RT_ROLL << 8); s.cdesc[NC + 2 * r + 1] = l | (RT_ROLL << 8) | (1 << 12); }
+      if (r < NROLL) { s.cdesc[NC + 2 * r] = l | (RT_ROLL << 8); s.cdesc[NC + 2 * r + 1] = l | (RT_ROLL << 8) | (1 << 12); }
     }
     fr0 = NC + NT;
     if (fr0 & 1) { if (l == 0) s.cdesc[fr0] = RT_PAD << 8; fr0++; }
     if (l < NC) { s.cdesc[fr0 + 2 * l] = l | (RT_FRIC << 8); s.cdesc[fr0 + 2 * l + 1] = l | (RT_FRIC << 8) | (1 << 12); }
     Rc = NC > 0 ? fr0 + 2 * NC : 0;
-    // Rc <= 16 + 6 + 32 = 54 = RC of the Golf scenes; the other scenes have no rolling friction (Rc <= 48)
+    // Rc <= NC_CAP + 2 * NROLL + 2 * NC_CAP = RC
   }
   gp.sync();
   // ---- per-lane row registers: slots [0, NSJ) joint rows, [NSJ, NS) contact rows
-  float w[NS], lam[NS], lamp[NS], rhs[NS], invd[NS], den[NS], lo[NS], hi[NS];
+  real w[NS], lam[NS], lamp[NS], rhs[NS], invd[NS], den[NS], lo[NS], hi[NS];
   int colown[NSJ], nidx[NSC];
 #pragma unroll
-  for (int k = 0; k < NS; k++) { w[k] = 0.f; lam[k] = 0.f; lamp[k] = 0.f; rhs[k] = 0.f; invd[k] = 0.f; den[k] = 0.f; lo[k] = 0.f; hi[k] = 0.f; }
+  for (int k = 0; k < NS; k++) { w[k] = 0._r; lam[k] = 0._r; lamp[k] = 0._r; rhs[k] = 0._r; invd[k] = 0._r; den[k] = 0._r; lo[k] = 0._r; hi[k] = 0._r; }
   // joint rows (signed form: a hi-limit row is the unit row with bounds [-max, 0])
 #pragma unroll
   for (int sj = 0; sj < NSJ; sj++) {
@@ -260,78 +267,78 @@ __device__ __noinline__ float solve_and_integrate(S& s, const DevModel& M, const
     if (j < n_nc) {
       const int dsc = s.jdesc[j], col = dsc & 255, type = (dsc >> 8) & 15, idx = dsc >> 12;
       colown[sj] = col;
-      const float dn = s.E[col * UG_NCOL + col], inv = 1.0f / dn;
+      const real dn = s.E[col * UG_NCOL + col], inv = 1.0_r / dn;
       den[sj] = dn; invd[sj] = inv;
-      const float vs = s.vstar[type == RT_GEAR ? 6 : idx], qi = s.q[type == RT_GEAR ? 6 : idx];
+      const real vs = s.vstar[type == RT_GEAR ? 6 : idx], qi = s.q[type == RT_GEAR ? 6 : idx];
       if (type == RT_LIM_LO) {
-        rhs[sj] = (-(qi - M.lower[idx]) * UGP_ERP * UGP_INV_DT - vs) * inv; lo[sj] = 0.f; hi[sj] = UGP_LIMIT_MAX_IMPULSE;
+        rhs[sj] = (-(qi - M.lower[idx]) * UGP_ERP * UGP_INV_DT - vs) * inv; lo[sj] = 0._r; hi[sj] = UGP_LIMIT_MAX_IMPULSE;
       } else if (type == RT_LIM_HI) {
-        rhs[sj] = ((M.upper[idx] - qi) * UGP_ERP * UGP_INV_DT - vs) * inv; lo[sj] = -UGP_LIMIT_MAX_IMPULSE; hi[sj] = 0.f;
+        rhs[sj] = ((M.upper[idx] - qi) * UGP_ERP * UGP_INV_DT - vs) * inv; lo[sj] = -UGP_LIMIT_MAX_IMPULSE; hi[sj] = 0._r;
       } else if (type == RT_MOTOR) {
-        float want = UGP_MOTOR_KP * (s.tgt[idx] - qi) * UGP_INV_DT + (1.0f - UGP_MOTOR_KD) * vs;
-        want = fminf(fmaxf(want, -M.velocity[idx]), M.velocity[idx]);
+        real want = UGP_MOTOR_KP * (s.tgt[idx] - qi) * UGP_INV_DT + (1.0_r - UGP_MOTOR_KD) * vs;
+        want = rmin(rmax(want, -M.velocity[idx]), M.velocity[idx]);
         rhs[sj] = (want - vs) * inv; lo[sj] = -M.effort[idx] * UGP_DT; hi[sj] = M.effort[idx] * UGP_DT;
       } else {
-        const int gd = c_gear_dof[idx]; const float gr = c_gear_ratio[idx];
-        float rel = vs + gr * s.vstar[gd];
-        float pe = UGP_GEAR_ERP * (qi + gr * s.q[gd]);
+        const int gd = c_gear_dof[idx]; const real gr = c_gear_ratio[idx];
+        real rel = vs + gr * s.vstar[gd];
+        real pe = UGP_GEAR_ERP * (qi + gr * s.q[gd]);
         rhs[sj] = (-pe * UGP_ERP * UGP_INV_DT - rel) * inv; lo[sj] = -UGP_GEAR_MAX_FORCE * UGP_DT; hi[sj] = UGP_GEAR_MAX_FORCE * UGP_DT;
       }
     }
   }
   // contact rows, pass 1 (one code copy, slot loop rolled): Jacobian, robot response (-> E), diagonal, right-hand
   // side. Row parameters go through a scratch area behind the M^-1 copy (dead dynamics temporaries).
-  float* const prm = &s.u.d.cm[0][0];
+  real* const prm = &s.u.d.cm[0][0];
 #pragma unroll 1
   for (int so = 0; so * G < Rc; so++) {
     const int c = l + G * so;
     if (c < Rc) {
       const int dsc = s.cdesc[c];
       const int type = (dsc >> 8) & 15, k = dsc & 255;
-      float4 p0 = make_float4(0.f, 0.f, 0.f, 0.f), p1 = make_float4(0.f, 0.f, 0.f, 0.f);
-      float* Er = s.E + (UG_NCOL + c) * UG_NCOL;
+      real4 p0 = make_real4(0._r, 0._r, 0._r, 0._r), p1 = make_real4(0._r, 0._r, 0._r, 0._r);
+      real* Er = s.E + (UG_NCOL + c) * UG_NCOL;
       if (type != RT_PAD) {
         CRow r; build_crow(s, M, dsc, r, true);
-        float Br[UG_NDOF];
+        real Br[UG_NDOF];
 #pragma unroll
         for (int a = 0; a < UG_NDOF; a++) {
-          const float4* Mr = reinterpret_cast<const float4*>(s.u.d.M[a]);
-          float4 m0 = Mr[0], m1 = Mr[1], m2 = Mr[2];
+          const real4* Mr = reinterpret_cast<const real4*>(s.u.d.M[a]);
+          real4 m0 = Mr[0], m1 = Mr[1], m2 = Mr[2];
           Br[a] = m0.x * r.Jr[0] + m0.y * r.Jr[1] + m0.z * r.Jr[2] + m0.w * r.Jr[3] + m1.x * r.Jr[4] + m1.y * r.Jr[5] + m1.z * r.Jr[6] + m1.w * r.Jr[7] +
                   m2.x * r.Jr[8] + m2.y * r.Jr[9] + m2.z * r.Jr[10] + m2.w * r.Jr[11];
         }
-        float dn = 0.f, rel = 0.f;
+        real dn = 0._r, rel = 0._r;
 #pragma unroll
         for (int a = 0; a < UG_NDOF; a++) { Er[a] = Br[a]; dn += r.Jr[a] * Br[a]; rel += r.Jr[a] * s.vstar[a]; }
 #pragma unroll
         for (int gi = 0; gi < 5; gi++) Er[12 + gi] = Br[6] + c_gear_ratio[gi] * Br[7 + gi];
         if (r.fa >= 0) {
-          const float* v = s.vstar + UG_NDOF + 6 * r.fa;
-          dn += dot(r.JlA, r.JlA) * (1.0f / M.fmass[r.fa]) + dot(r.JaA, symv(s.fIinv[r.fa], r.JaA));
+          const real* v = s.vstar + UG_NDOF + 6 * r.fa;
+          dn += dot(r.JlA, r.JlA) * (1.0_r / M.fmass[r.fa]) + dot(r.JaA, symv(s.fIinv[r.fa], r.JaA));
           rel += dot(r.JlA, ld3(v)) + dot(r.JaA, ld3(v + 3));
         }
         if (r.fb >= 0) {
-          const float* v = s.vstar + UG_NDOF + 6 * r.fb;
-          dn += dot(r.JlB, r.JlB) * (1.0f / M.fmass[r.fb]) + dot(r.JaB, symv(s.fIinv[r.fb], r.JaB));
+          const real* v = s.vstar + UG_NDOF + 6 * r.fb;
+          dn += dot(r.JlB, r.JlB) * (1.0_r / M.fmass[r.fb]) + dot(r.JaB, symv(s.fIinv[r.fb], r.JaB));
           rel += dot(r.JlB, ld3(v)) + dot(r.JaB, ld3(v + 3));
         }
-        const float inv = 1.0f / dn;
+        const real inv = 1.0_r / dn;
         p0.y = inv; p0.z = dn;
         const Con& cn = s.con[k];
         if (type == RT_NORMAL) {
-          float pen = cn.dist + UGP_LINEAR_SLOP, rest = 0.f;
-          if (fabsf(rel) >= UGP_RESTITUTION_VEL_THRESHOLD) rest = fmaxf(cn.rest * -rel, 0.f);
-          float pos_e = 0.f, vel_e = rest - rel;
-          if (pen > 0.f) vel_e -= pen * UGP_INV_DT; else pos_e = -pen * UGP_ERP2 * UGP_INV_DT;
-          p0.x = (pos_e + vel_e) * inv; p0.w = 0.f; p1.x = 1e10f;
+          real pen = cn.dist + UGP_LINEAR_SLOP, rest = 0._r;
+          if (rabs(rel) >= UGP_RESTITUTION_VEL_THRESHOLD) rest = rmax(cn.rest * -rel, 0._r);
+          real pos_e = 0._r, vel_e = rest - rel;
+          if (pen > 0._r) vel_e -= pen * UGP_INV_DT; else pos_e = -pen * UGP_ERP2 * UGP_INV_DT;
+          p0.x = (pos_e + vel_e) * inv; p0.w = 0._r; p1.x = 1e10_r;
         } else {
-          p0.x = -rel * inv; p1.x = type == RT_ROLL ? cn.roll : cn.mu; p1.y = __int_as_float(k);
+          p0.x = -rel * inv; p1.x = type == RT_ROLL ? cn.roll : cn.mu; p1.y = (real)k;
         }
       } else {
 #pragma unroll
-        for (int a = 0; a < UG_NCOL; a++) Er[a] = 0.f;
+        for (int a = 0; a < UG_NCOL; a++) Er[a] = 0._r;
       }
-      reinterpret_cast<float4*>(prm)[2 * c] = p0; reinterpret_cast<float4*>(prm)[2 * c + 1] = p1;
+      reinterpret_cast<real4*>(prm)[2 * c] = p0; reinterpret_cast<real4*>(prm)[2 * c + 1] = p1;
     }
   }
 #pragma unroll
@@ -339,8 +346,8 @@ __device__ __noinline__ float solve_and_integrate(S& s, const DevModel& M, const
     const int c = l + G * so;
     nidx[so] = 0;
     if (c < Rc) {
-      float4 p0 = reinterpret_cast<const float4*>(prm)[2 * c], p1 = reinterpret_cast<const float4*>(prm)[2 * c + 1];
-      rhs[NSJ + so] = p0.x; invd[NSJ + so] = p0.y; den[NSJ + so] = p0.z; lo[NSJ + so] = p0.w; hi[NSJ + so] = p1.x; nidx[so] = __float_as_int(p1.y);
+      real4 p0 = reinterpret_cast<const real4*>(prm)[2 * c], p1 = reinterpret_cast<const real4*>(prm)[2 * c + 1];
+      rhs[NSJ + so] = p0.x; invd[NSJ + so] = p0.y; den[NSJ + so] = p0.z; lo[NSJ + so] = p0.w; hi[NSJ + so] = p1.x; nidx[so] = (int)p1.y;
     }
   }
   gp.sync();
@@ -357,26 +364,26 @@ __device__ __noinline__ float solve_and_integrate(S& s, const DevModel& M, const
 #pragma unroll
     for (int b = 0; b < UG_MAXFREE; b++) { dl[b] = mk3(0, 0, 0); da[b] = mk3(0, 0, 0); }
 #pragma unroll
-    for (int d = 0; d < UG_NDOF; d++) r.Jr[d] = 0.f;
+    for (int d = 0; d < UG_NDOF; d++) r.Jr[d] = 0._r;
     if (((dsc >> 8) & 15) != RT_PAD) {
       build_crow(s, M, dsc, r, true);
 #pragma unroll
       for (int b = 0; b < UG_MAXFREE; b++) {
-        if (r.fa == b) { dl[b] = r.JlA * (1.0f / M.fmass[b]); da[b] = symv(s.fIinv[b], r.JaA); }
-        if (r.fb == b) { dl[b] = r.JlB * (1.0f / M.fmass[b]); da[b] = symv(s.fIinv[b], r.JaB); }
+        if (r.fa == b) { dl[b] = r.JlA * (1.0_r / M.fmass[b]); da[b] = symv(s.fIinv[b], r.JaA); }
+        if (r.fb == b) { dl[b] = r.JlB * (1.0_r / M.fmass[b]); da[b] = symv(s.fIinv[b], r.JaB); }
       }
     }
     const int cmax = min(Rc, so * G + G);
-    float* Trow = s.u.T + c * RC;
+    real* Trow = s.u.T + c * RC;
 #pragma unroll 1
     for (int cp = 0; cp < cmax; cp++) {
       const int dp = s.cdesc[cp], tp = (dp >> 8) & 15;
-      float acc = 0.f;
+      real acc = 0._r;
       if (tp != RT_PAD) {
         const Con& cn = s.con[dp & 255];
         f3 n = ld3(cn.n), t1, t2; plane_space(n, t1, t2);
         f3 dv = tp == RT_NORMAL ? n : ((dp >> 12) == 0 ? t1 : t2);
-        const float* Ep = s.E + (UG_NCOL + cp) * UG_NCOL;
+        const real* Ep = s.E + (UG_NCOL + cp) * UG_NCOL;
 #pragma unroll
         for (int d = 0; d < UG_NDOF; d++) acc += r.Jr[d] * Ep[d];
         const int bod = cn.bodies, fa = (bod & 255) - 1, fb = ((bod >> 8) & 255) - 1;
@@ -401,12 +408,12 @@ __device__ __noinline__ float solve_and_integrate(S& s, const DevModel& M, const
   const unsigned aE = smem_u32(s.E), aT = smem_u32(s.u.T);
   unsigned aEj[NSJ], aEq[NSJ];
 #pragma unroll
-  for (int k = 0; k < NSJ; k++) { aEj[k] = aE + 4u * (unsigned)(colown[k] * UG_NCOL); aEq[k] = aE + 4u * (unsigned)(UG_NCOL * UG_NCOL + colown[k]); }
-  const unsigned aEc = aE + 4u * (unsigned)((UG_NCOL + l) * UG_NCOL);  // contact slot o: + o * G * UG_NCOL * 4
-  const unsigned aTl = aT + 4u * (unsigned)l;                           // row r: + r * RC * 4; contact slot o: + o * G * 4
-  float limv[NSC];
+  for (int k = 0; k < NSJ; k++) { aEj[k] = aE + UG_RB * (unsigned)(colown[k] * UG_NCOL); aEq[k] = aE + UG_RB * (unsigned)(UG_NCOL * UG_NCOL + colown[k]); }
+  const unsigned aEc = aE + UG_RB * (unsigned)((UG_NCOL + l) * UG_NCOL);  // contact slot o: + o * G * UG_NCOL * 4
+  const unsigned aTl = aT + UG_RB * (unsigned)l;                           // row r: + r * RC * 4; contact slot o: + o * G * 4
+  real limv[NSC];
 #pragma unroll
-  for (int so = 0; so < NSC; so++) limv[so] = 0.f;
+  for (int so = 0; so < NSC; so++) limv[so] = 0._r;
   // Operand loads are written BEFORE the clamp / shuffle chain of each step on purpose: every shuffle ends a basic
   // block (convergence check), ptxas does not move loads across it, and a load issued after the shuffle would put
   // its ~29-cycle latency on the step's critical path. Issued first, it overlaps the chain (profiles/ r01d -> r01e).
@@ -417,32 +424,32 @@ __device__ __noinline__ float solve_and_integrate(S& s, const DevModel& M, const
 #define UG_JOINT_STEP(ROW, NEXT, SJ, NACT)                                                               \
   {                                                                                                      \
     const unsigned ci_ = ci_cur;                                                                         \
-    float ej_[NSJ], ec_[NACT > 0 ? NACT : 1];                                                            \
+    real ej_[NSJ], ec_[NACT > 0 ? NACT : 1];                                                            \
     _Pragma("unroll") for (int k_ = 0; k_ < NSJ; k_++) ej_[k_] = lds(aEj[k_] + ci_);                     \
-    _Pragma("unroll") for (int o_ = 0; o_ < (NACT); o_++) ec_[o_] = lds(aEc + ci_ + 4u * (unsigned)(o_ * G * UG_NCOL)); \
+    _Pragma("unroll") for (int o_ = 0; o_ < (NACT); o_++) ec_[o_] = lds(aEc + ci_ + UG_RB * (unsigned)(o_ * G * UG_NCOL)); \
     ci_cur = (unsigned)s.jci4[(NEXT) + 1];                                                               \
     const int li_ = (ROW) - (SJ) * G;                                                                    \
-    float d_ = fmaf(-w[SJ], invd[SJ], rhs[SJ]);                                                          \
-    d_ = fminf(fmaxf(d_, jlo[SJ]), jhi[SJ]);                                                             \
-    const float delta = gp.shfl(d_, li_);                                                                \
+    real d_ = rfma(-w[SJ], invd[SJ], rhs[SJ]);                                                          \
+    d_ = rmin(rmax(d_, jlo[SJ]), jhi[SJ]);                                                             \
+    const real delta = gp.shfl(d_, li_);                                                                \
     if (l == li_) lam[SJ] += delta;                                                                      \
-    _Pragma("unroll") for (int k_ = 0; k_ < NSJ; k_++) w[k_] = fmaf(ej_[k_], delta, w[k_]);              \
-    _Pragma("unroll") for (int o_ = 0; o_ < (NACT); o_++) w[NSJ + o_] = fmaf(ec_[o_], delta, w[NSJ + o_]); \
+    _Pragma("unroll") for (int k_ = 0; k_ < NSJ; k_++) w[k_] = rfma(ej_[k_], delta, w[k_]);              \
+    _Pragma("unroll") for (int o_ = 0; o_ < (NACT); o_++) w[NSJ + o_] = rfma(ec_[o_], delta, w[NSJ + o_]); \
   }
   // operands of a contact-row step (rows ROW and, when PAIR, ROW + 1): E entries for the joint slots, T entries for
   // the contact slots
 #define UG_CONTACT_LOAD(ROW, PAIR, NACT)                                                                 \
-    const unsigned er_ = 4u * (unsigned)((ROW) * UG_NCOL), tr_ = aTl + 4u * (unsigned)((ROW) * RC);      \
-    float uj_[NSJ], vj_[NSJ], uc_[NACT], vc_[NACT];                                                      \
-    _Pragma("unroll") for (int k_ = 0; k_ < NSJ; k_++) { uj_[k_] = lds(aEq[k_] + er_); vj_[k_] = (PAIR) ? lds(aEq[k_] + er_ + 4u * UG_NCOL) : 0.f; } \
-    _Pragma("unroll") for (int o_ = 0; o_ < (NACT); o_++) { uc_[o_] = lds(tr_ + 4u * (unsigned)(o_ * G)); vc_[o_] = (PAIR) ? lds(tr_ + 4u * (unsigned)(RC + o_ * G)) : 0.f; }
+    const unsigned er_ = UG_RB * (unsigned)((ROW) * UG_NCOL), tr_ = aTl + UG_RB * (unsigned)((ROW) * RC);      \
+    real uj_[NSJ], vj_[NSJ], uc_[NACT], vc_[NACT];                                                      \
+    _Pragma("unroll") for (int k_ = 0; k_ < NSJ; k_++) { uj_[k_] = lds(aEq[k_] + er_); vj_[k_] = (PAIR) ? lds(aEq[k_] + er_ + UG_RB * UG_NCOL) : 0._r; } \
+    _Pragma("unroll") for (int o_ = 0; o_ < (NACT); o_++) { uc_[o_] = lds(tr_ + UG_RB * (unsigned)(o_ * G)); vc_[o_] = (PAIR) ? lds(tr_ + UG_RB * (unsigned)(RC + o_ * G)) : 0._r; }
 #define UG_CONTACT_APPLY(DA, DB, PAIR, NACT)                                                             \
-    _Pragma("unroll") for (int k_ = 0; k_ < NSJ; k_++) { w[k_] = fmaf(uj_[k_], DA, w[k_]); if (PAIR) w[k_] = fmaf(vj_[k_], DB, w[k_]); } \
-    _Pragma("unroll") for (int o_ = 0; o_ < (NACT); o_++) { w[NSJ + o_] = fmaf(uc_[o_], DA, w[NSJ + o_]); if (PAIR) w[NSJ + o_] = fmaf(vc_[o_], DB, w[NSJ + o_]); }
+    _Pragma("unroll") for (int k_ = 0; k_ < NSJ; k_++) { w[k_] = rfma(uj_[k_], DA, w[k_]); if (PAIR) w[k_] = rfma(vj_[k_], DB, w[k_]); } \
+    _Pragma("unroll") for (int o_ = 0; o_ < (NACT); o_++) { w[NSJ + o_] = rfma(uc_[o_], DA, w[NSJ + o_]); if (PAIR) w[NSJ + o_] = rfma(vc_[o_], DB, w[NSJ + o_]); }
   // joint rows, order alternates with the iteration parity (backward on even sweeps)
 #define UG_JOINT_SWEEP(NACT)                                                                             \
   /* a lane's impulse changes only at its own step, so its clamp bounds are constant over the sweep */  \
-  float jlo[NSJ], jhi[NSJ];                                                                              \
+  real jlo[NSJ], jhi[NSJ];                                                                              \
   _Pragma("unroll") for (int k_ = 0; k_ < NSJ; k_++) { jlo[k_] = lo[k_] - lam[k_]; jhi[k_] = hi[k_] - lam[k_]; } \
   if (it & 1) {                                                                                          \
     unsigned ci_cur = (unsigned)s.jci4[1];                                                               \
@@ -460,19 +467,19 @@ __device__ __noinline__ float solve_and_integrate(S& s, const DevModel& M, const
       if (row >= sj * G) UG_JOINT_STEP(row, row - 1, sj, NACT)                                           \
     }                                                                                                    \
   }
-  // normals (contacts 0..NC-1 live in contact slot 0: NC <= 16 <= G), friction limits from this sweep's normal
+  // normals (contacts 0..NC-1 live in contact slot 0: NC <= NC_CAP <= G), friction limits from this sweep's normal
   // impulses, rolling-friction rows (Golf only; skipped while the normal impulse is zero), friction pairs with the
   // implicit cone
 #define UG_CONTACT_SWEEP(NACT)                                                                           \
   {                                                                                                      \
-    const float nlo = lo[NSJ] - lam[NSJ], nhi = hi[NSJ] - lam[NSJ];   /* constant over the sweep, as above */ \
+    const real nlo = lo[NSJ] - lam[NSJ], nhi = hi[NSJ] - lam[NSJ];   /* constant over the sweep, as above */ \
     _Pragma("unroll 1") for (int row = 0; row < NC; row++) {                                             \
       UG_CONTACT_LOAD(row, false, NACT)                                                                  \
-      float d_ = fmaf(-w[NSJ], invd[NSJ], rhs[NSJ]);                                                     \
-      d_ = fminf(fmaxf(d_, nlo), nhi);                                                                   \
-      const float delta = gp.shfl(d_, row);                                                              \
+      real d_ = rfma(-w[NSJ], invd[NSJ], rhs[NSJ]);                                                     \
+      d_ = rmin(rmax(d_, nlo), nhi);                                                                   \
+      const real delta = gp.shfl(d_, row);                                                              \
       if (l == row) lam[NSJ] += delta;                                                                   \
-      UG_CONTACT_APPLY(delta, 0.f, false, NACT)                                                          \
+      UG_CONTACT_APPLY(delta, 0._r, false, NACT)                                                          \
     }                                                                                                    \
     _Pragma("unroll") for (int so = 0; so < (NACT); so++) limv[so] = hi[NSJ + so] * gp.shfl(lam[NSJ], nidx[so]); \
     if (NT > 0) {                                                                                        \
@@ -480,13 +487,13 @@ __device__ __noinline__ float solve_and_integrate(S& s, const DevModel& M, const
         const int a_ = max(NC, so * G), b_ = min(NC + NT, so * G + G);                                   \
         _Pragma("unroll 1") for (int row = a_; row < b_; row++) {                                        \
           UG_CONTACT_LOAD(row, false, NACT)                                                              \
-          const float bnd = limv[so];                                                                    \
-          float d_ = fmaf(-w[NSJ + so], invd[NSJ + so], rhs[NSJ + so]);                                  \
-          d_ = fminf(fmaxf(d_, -bnd - lam[NSJ + so]), bnd - lam[NSJ + so]);                              \
-          if (!(bnd > 0.f)) d_ = 0.f;                                                                    \
-          const float delta = gp.shfl(d_, row - so * G);                                                 \
+          const real bnd = limv[so];                                                                    \
+          real d_ = rfma(-w[NSJ + so], invd[NSJ + so], rhs[NSJ + so]);                                  \
+          d_ = rmin(rmax(d_, -bnd - lam[NSJ + so]), bnd - lam[NSJ + so]);                              \
+          if (!(bnd > 0._r)) d_ = 0._r;                                                                    \
+          const real delta = gp.shfl(d_, row - so * G);                                                 \
           if (l == row - so * G) lam[NSJ + so] += delta;                                                 \
-          UG_CONTACT_APPLY(delta, 0.f, false, NACT)                                                      \
+          UG_CONTACT_APPLY(delta, 0._r, false, NACT)                                                      \
         }                                                                                                \
       }                                                                                                  \
     }                                                                                                    \
@@ -495,18 +502,18 @@ __device__ __noinline__ float solve_and_integrate(S& s, const DevModel& M, const
       _Pragma("unroll 1") for (int row = a_; row < b_; row += 2) {                                       \
         UG_CONTACT_LOAD(row, true, NACT)                                                                 \
         const int li = row - so * G;                                                                     \
-        float d_ = fmaf(-w[NSJ + so], invd[NSJ + so], rhs[NSJ + so]);                                    \
-        const float sm = lam[NSJ + so] + d_;                                                             \
-        const float ot = __shfl_xor_sync(gp.mask, sm, 1, G); /* the pair's other tangent (pairs start on even rows) */ \
-        const float lm = limv[so];                           /* both lanes of a pair carry the same limit */ \
+        real d_ = rfma(-w[NSJ + so], invd[NSJ + so], rhs[NSJ + so]);                                    \
+        const real sm = lam[NSJ + so] + d_;                                                             \
+        const real ot = __shfl_xor_sync(gp.mask, sm, 1, G); /* the pair's other tangent (pairs start on even rows) */ \
+        const real lm = limv[so];                           /* both lanes of a pair carry the same limit */ \
         /* implicit cone, branch-free: inside the box |.| <= lm both tangents keep their value, else this one is */ \
         /* scaled onto the circle of radius lm (rsqrt.approx.ftz: the argument is >= lm^2 > 0 whenever it is used) */ \
-        const float cs = fabsf(lm * sm * rsqrt_ftz(fmaxf(fmaf(sm, sm, ot * ot), 1e-30f)));               \
-        const float cl = fmaxf(fabsf(sm), fabsf(ot)) > lm ? cs : lm;                                     \
-        const float sn = fminf(fmaxf(sm, -cl), cl);                                                      \
+        const real cs = rabs(lm * sm * rsqrt_ftz(rmax(rfma(sm, sm, ot * ot), 1e-30_r)));               \
+        const real cl = rmax(rabs(sm), rabs(ot)) > lm ? cs : lm;                                     \
+        const real sn = rmin(rmax(sm, -cl), cl);                                                      \
         d_ = sn - lam[NSJ + so];                                                                         \
         if ((l | 1) == (li | 1)) lam[NSJ + so] = sn;                                                     \
-        const float dA = gp.shfl(d_, li), dB = gp.shfl(d_, li + 1);                                      \
+        const real dA = gp.shfl(d_, li), dB = gp.shfl(d_, li + 1);                                      \
         UG_CONTACT_APPLY(dA, dB, true, NACT)                                                             \
       }                                                                                                  \
     }                                                                                                    \
@@ -537,9 +544,9 @@ __device__ __noinline__ float solve_and_integrate(S& s, const DevModel& M, const
     else if (NSC >= 4) { UG_JOINT_SWEEP(4) UG_CONTACT_SWEEP(4) }
     it++;
     // least-squares residual of the sweep: max over rows of the squared velocity change (Bullet's early exit)
-    float res = 0.f;
+    real res = 0._r;
 #pragma unroll
-    for (int k = 0; k < NS; k++) { float r_ = (lam[k] - lamp[k]) * den[k]; res = fmaxf(res, r_ * r_); lamp[k] = lam[k]; }
+    for (int k = 0; k < NS; k++) { real r_ = (lam[k] - lamp[k]) * den[k]; res = rmax(res, r_ * r_); lamp[k] = lam[k]; }
     if (!gp.any(res > UGP_RESIDUAL_THRESHOLD)) break;  // max over the rows <= threshold, as one vote
   }
 #undef UG_JOINT_STEP
@@ -564,7 +571,7 @@ __device__ __noinline__ float solve_and_integrate(S& s, const DevModel& M, const
       const int dsc = s.cdesc[c];
       if (((dsc >> 8) & 15) != RT_PAD) {
         CRow r; build_crow(s, M, dsc, r, false);
-        const float lm = s.lam[UG_JMAX + c];
+        const real lm = s.lam[UG_JMAX + c];
 #pragma unroll
         for (int b = 0; b < UG_MAXFREE; b++) {
           if (r.fa == b) { gl[b] = gl[b] + r.JlA * lm; ga[b] = ga[b] + r.JaA * lm; }
@@ -578,31 +585,31 @@ __device__ __noinline__ float solve_and_integrate(S& s, const DevModel& M, const
       ga[b] = mk3(gp.sum(ga[b].x), gp.sum(ga[b].y), gp.sum(ga[b].z));
     }
   }
-  float absq = 0.f;
+  real absq = 0._r;
   if (l < UG_NDOF) {
-    float dv = 0.f;
+    real dv = 0._r;
 #pragma unroll 1
-    for (int j = 0; j < n_nc; j++) dv = fmaf(s.lam[j], s.E[(s.jdesc[j] & 255) * UG_NCOL + l], dv);
+    for (int j = 0; j < n_nc; j++) dv = rfma(s.lam[j], s.E[(s.jdesc[j] & 255) * UG_NCOL + l], dv);
 #pragma unroll 1
-    for (int c = 0; c < Rc; c++) dv = fmaf(s.lam[UG_JMAX + c], s.E[(UG_NCOL + c) * UG_NCOL + l], dv);
-    float v = fminf(fmaxf(s.vstar[l] + dv, -UGP_MAX_COORD_VEL), UGP_MAX_COORD_VEL);
+    for (int c = 0; c < Rc; c++) dv = rfma(s.lam[UG_JMAX + c], s.E[(UG_NCOL + c) * UG_NCOL + l], dv);
+    real v = rmin(rmax(s.vstar[l] + dv, -UGP_MAX_COORD_VEL), UGP_MAX_COORD_VEL);
     s.qd[l] = v; s.q[l] += UGP_DT * v;
-    absq = fabsf(UGP_DT * v);
+    absq = rabs(UGP_DT * v);
   } else if (l < UG_NDOF + UG_MAXFREE) {
     int b = l - UG_NDOF;
     if (b < M.nfree && (s.flags & (FL_BODY0 << b))) {
-      const float* vb = s.vstar + UG_NDOF + 6 * b;
-      float im = 1.0f / M.fmass[b];
+      const real* vb = s.vstar + UG_NDOF + 6 * b;
+      real im = 1.0_r / M.fmass[b];
       f3 lin = ld3(vb) + pick3(gl, b) * im;
       f3 ang = ld3(vb + 3) + symv(s.fIinv[b], pick3(ga, b));
       st3(s.flin[b], lin); st3(s.fang[b], ang);
       st3(s.fpos[b], ld3(s.fpos[b]) + lin * UGP_DT);
-      float wn = norm3(ang);
+      real wn = norm3(ang);
       if (wn * UGP_DT > UGP_ANGULAR_MOTION_THRESHOLD) wn = UGP_ANGULAR_MOTION_THRESHOLD * UGP_INV_DT;
       f3 axv;
-      if (wn < 0.001f) axv = ang * (0.5f * UGP_DT - UGP_DT * UGP_DT * UGP_DT * 0.020833333333f * wn * wn);
-      else axv = ang * (sinf(0.5f * wn * UGP_DT) / wn);
-      q4 qn = qnormalize(qmul(mkq(axv.x, axv.y, axv.z, cosf(0.5f * wn * UGP_DT)), mkq(s.fquat[b][0], s.fquat[b][1], s.fquat[b][2], s.fquat[b][3])));
+      if (wn < 0.001_r) axv = ang * (0.5_r * UGP_DT - UGP_DT * UGP_DT * UGP_DT * 0.020833333333_r * wn * wn);
+      else axv = ang * (rsin(0.5_r * wn * UGP_DT) / wn);
+      q4 qn = qnormalize(qmul(mkq(axv.x, axv.y, axv.z, rcos(0.5_r * wn * UGP_DT)), mkq(s.fquat[b][0], s.fquat[b][1], s.fquat[b][2], s.fquat[b][3])));
       s.fquat[b][0] = qn.x; s.fquat[b][1] = qn.y; s.fquat[b][2] = qn.z; s.fquat[b][3] = qn.w;
     }
   }
@@ -614,7 +621,7 @@ __device__ __noinline__ float solve_and_integrate(S& s, const DevModel& M, const
 
 // One stepSimulation tick. Returns sum over joints of |q(t) - q(t-1)|.
 template <int G, int RC, class S>
-UG_DEV float tick(S& s, const DevModel& M, const Gp<G>& gp, int* iters) {
+UG_DEV real tick(S& s, const DevModel& M, const Gp<G>& gp, int* iters) {
   UG_T0();
   fk_bodies(s, M, gp);
   UG_TP(0)

@@ -5,12 +5,17 @@
 #pragma once
 #include <stdint.h>
 
+#include "real.h"
+
 #define UG_NDOF 12
 #define UG_NLINK 19
 #define UG_MAXFREE 3
 #define UG_MAXSHAPES 32
-#define UG_MAXPAIRS 128
-#define UG_MAXC 16
+#define UG_MAXPAIRS 160
+#define UG_HITWORDS ((UG_MAXPAIRS + 31) / 32)
+// Manifold-point capacity of a tick is a per-scene template constant of the kernel (kernels.cuh: EnvNC, 16 / 24 / 32 from
+// the measured distributions, tools/contact_hist.py); UG_MAXC is the width of the contact-point export and the largest of them.
+#define UG_MAXC 32
 #define UG_STATE 96
 #define UG_ENV_COUNT 7  // 0 BallBalance 1 TwoBallsBalance 2 CubesPush 3 CubesGrasp 4 Golf 5 CubesPushDiff 6 GolfJoints
 
@@ -19,26 +24,29 @@ struct DevShape {
   int body;    // 0 robot, 1..3 free body, -1 static
   int link;    // Bullet link index (robot) or sub-shape id
   int rbody;   // robot shapes: index of the movable body (dof) that carries the link
-  float lc[3]; float lR[9];  // local centre / rotation in the carrying body's frame (static: world)
-  float half[3]; float radius;
-  float mu, rest, roll, cbt, brad;
+  real lc[3]; real lR[9];  // local centre / rotation in the carrying body's frame (static: world)
+  real half[3]; real radius;
+  real mu, rest, roll, cbt, brad;
 };
 
-struct DevSub { float mass; float com[3]; float I[6]; };  // I: xx xy xz yy yz zz about the sub-link COM, body frame
+struct DevSub { real mass; real com[3]; real I[6]; };  // I: xx xy xz yy yz zz about the sub-link COM, body frame
 
 struct DevModel {
   int par[UG_NDOF]; uint32_t anc[UG_NDOF]; uint32_t sub[UG_NDOF]; int axis[UG_NDOF];
-  float jpos[UG_NDOF][3]; float jrot[UG_NDOF][9];
-  float mass[UG_NDOF]; float com[UG_NDOF][3]; float I[UG_NDOF][6];
+  real jpos[UG_NDOF][3]; real jrot[UG_NDOF][9];
+  real mass[UG_NDOF]; real com[UG_NDOF][3]; real I[UG_NDOF][6];
   int nsub[UG_NDOF]; DevSub subl[UG_NDOF][3];
-  float lower[UG_NDOF], upper[UG_NDOF], effort[UG_NDOF], velocity[UG_NDOF];
-  int link_body[UG_NLINK]; float link_lpos[UG_NLINK][3]; float link_lrot[UG_NLINK][9];
-  float link_jquat[UG_NLINK][4]; float link_jxyz[UG_NLINK][3]; int link_parent[UG_NLINK]; int link_dof[UG_NLINK]; int link_axis[UG_NLINK];
-  float aabb_c[2][3], aabb_h[2][3];  // collision AABBs of links 11 and 16 in their link frames
-  int env_type, nfree, nshapes, npairs, obs_dim, act_dim, max_steps; float gravity;
+  real lower[UG_NDOF], upper[UG_NDOF], effort[UG_NDOF], velocity[UG_NDOF];
+  int link_body[UG_NLINK]; real link_lpos[UG_NLINK][3]; real link_lrot[UG_NLINK][9];
+  real link_jquat[UG_NLINK][4]; real link_jxyz[UG_NLINK][3]; int link_parent[UG_NLINK]; int link_dof[UG_NLINK]; int link_axis[UG_NLINK];
+  real aabb_c[2][3], aabb_h[2][3];  // collision AABBs of links 11 and 16 in their link frames
+  int env_type, nfree, nshapes, npairs, obs_dim, act_dim, max_steps; real gravity;
   int generic_sweeps;  // 1: contact-free ticks take the generic sweeps too (URGYM_GENERIC_SWEEPS=1 at create; comparison runs and tests)
-  float fmass[UG_MAXFREE]; float finertia[UG_MAXFREE][3];
+  real fmass[UG_MAXFREE]; real finertia[UG_MAXFREE][3];
   DevShape shapes[UG_MAXSHAPES]; uint8_t pairs[UG_MAXPAIRS][2];
+  // broad-phase bound per pair: the pair can only produce manifold points (separating-axis slack <= margin on all 15 axes)
+  // while the centre distance (static partner: distance from the centre to the static box) is <= cullr (model_build.cpp)
+  real cullr[UG_MAXPAIRS];
 };
 
 // Host: fills *m for env_type 0..UG_ENV_COUNT-1. Returns 0 or -1.

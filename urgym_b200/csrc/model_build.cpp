@@ -36,21 +36,21 @@ void mat_to_quat(const DM& R, double* q) {
 DevShape mk_box(int body, int link, const double* lc, const double* half, double mu, double rest = 0, double roll = 0) {
   DevShape s; std::memset(&s, 0, sizeof(s));
   s.kind = 0; s.body = body; s.link = link; s.rbody = -1;
-  for (int i = 0; i < 3; i++) { s.lc[i] = (float)lc[i]; s.half[i] = (float)half[i]; }
+  for (int i = 0; i < 3; i++) { s.lc[i] = (real)lc[i]; s.half[i] = (real)half[i]; }
   for (int i = 0; i < 9; i++) s.lR[i] = (i % 4 == 0);
   double n = std::sqrt(half[0] * half[0] + half[1] * half[1] + half[2] * half[2]);
-  s.mu = (float)mu; s.rest = (float)rest; s.roll = (float)roll; s.cbt = (float)(UGP_CONTACT_BREAKING * n); s.brad = (float)n;
+  s.mu = (real)mu; s.rest = (real)rest; s.roll = (real)roll; s.cbt = (real)(UGP_CONTACT_BREAKING * n); s.brad = (real)n;
   return s;
 }
 DevShape mk_sphere(int body, int link, double r, double mu, double rest = 0, double roll = 0) {
   double z[3] = {0, 0, 0}, h[3] = {r, r, r};
   DevShape s = mk_box(body, link, z, h, mu, rest, roll);
-  s.kind = 1; s.radius = (float)r; s.cbt = (float)(UGP_CONTACT_BREAKING * r); s.brad = (float)r;
+  s.kind = 1; s.radius = (real)r; s.cbt = (real)(UGP_CONTACT_BREAKING * r); s.brad = (real)r;
   return s;
 }
-void box_inertia(double m, const double* h, float* out) {
+void box_inertia(double m, const double* h, real* out) {
   double lx = 2 * h[0], ly = 2 * h[1], lz = 2 * h[2];
-  out[0] = (float)(m / 12 * (ly * ly + lz * lz)); out[1] = (float)(m / 12 * (lx * lx + lz * lz)); out[2] = (float)(m / 12 * (lx * lx + ly * ly));
+  out[0] = (real)(m / 12 * (ly * ly + lz * lz)); out[1] = (real)(m / 12 * (lx * lx + lz * lz)); out[2] = (real)(m / 12 * (lx * lx + ly * ly));
 }
 
 }  // namespace
@@ -79,11 +79,11 @@ int build_model(int env_type_full, DevModel* m) {
       lrot[i] = mm(pr, jr);
     }
     m->link_body[i] = carrier[i];
-    for (int k = 0; k < 3; k++) m->link_lpos[i][k] = (float)lpos[i].v[k];
-    for (int k = 0; k < 9; k++) m->link_lrot[i][k] = (float)lrot[i].m[k];
+    for (int k = 0; k < 3; k++) m->link_lpos[i][k] = (real)lpos[i].v[k];
+    for (int k = 0; k < 9; k++) m->link_lrot[i][k] = (real)lrot[i].m[k];
     double q[4]; mat_to_quat(jr, q);
-    for (int k = 0; k < 4; k++) m->link_jquat[i][k] = (float)q[k];
-    for (int k = 0; k < 3; k++) m->link_jxyz[i][k] = (float)L.jxyz[k];
+    for (int k = 0; k < 4; k++) m->link_jquat[i][k] = (real)q[k];
+    for (int k = 0; k < 3; k++) m->link_jxyz[i][k] = (real)L.jxyz[k];
     m->link_parent[i] = L.parent; m->link_dof[i] = dof_of_link[i];
     m->link_axis[i] = L.axis[0] > 0.5 ? 0 : (L.axis[1] > 0.5 ? 1 : 2);
   }
@@ -97,11 +97,11 @@ int build_model(int env_type_full, DevModel* m) {
     D3 jx = {{L.jxyz[0], L.jxyz[1], L.jxyz[2]}}; D3 o = mv(pr, jx);
     DM jr; for (int k = 0; k < 9; k++) jr.m[k] = L.jrot[k];
     DM r = mm(pr, jr);
-    for (int k = 0; k < 3; k++) m->jpos[d][k] = (float)(pp.v[k] + o.v[k]);
-    for (int k = 0; k < 9; k++) m->jrot[d][k] = (float)r.m[k];
+    for (int k = 0; k < 3; k++) m->jpos[d][k] = (real)(pp.v[k] + o.v[k]);
+    for (int k = 0; k < 9; k++) m->jrot[d][k] = (real)r.m[k];
     if (!((L.axis[0] == 1 && L.axis[1] == 0 && L.axis[2] == 0) || (L.axis[0] == 0 && L.axis[1] == 1 && L.axis[2] == 0) || (L.axis[0] == 0 && L.axis[1] == 0 && L.axis[2] == 1))) return -1;
     m->axis[d] = L.axis[0] == 1 ? 0 : (L.axis[1] == 1 ? 1 : 2);
-    m->lower[d] = (float)L.lower; m->upper[d] = (float)L.upper; m->effort[d] = (float)L.effort; m->velocity[d] = (float)L.velocity;
+    m->lower[d] = (real)L.lower; m->upper[d] = (real)L.upper; m->effort[d] = (real)L.effort; m->velocity[d] = (real)L.velocity;
   }
   for (int d = 0; d < UG_NDOF; d++) for (int e = 0; e < UG_NDOF; e++) if (m->anc[e] >> d & 1) m->sub[d] |= 1u << e;
   // merged mass properties and per-sub-link data
@@ -119,8 +119,8 @@ int build_model(int env_type_full, DevModel* m) {
       M += L.mass;
       for (int a = 0; a < 3; a++) for (int b = 0; b < 3; b++) { double v = 0; for (int k = 0; k < 3; k++) v += lrot[i].m[3 * a + k] * L.inertia[k] * lrot[i].m[3 * b + k]; sI[s][3 * a + b] = v; }
       DevSub& S = m->subl[d][s];
-      S.mass = (float)L.mass; for (int k = 0; k < 3; k++) S.com[k] = (float)sc[s][k];
-      S.I[0] = (float)sI[s][0]; S.I[1] = (float)sI[s][1]; S.I[2] = (float)sI[s][2]; S.I[3] = (float)sI[s][4]; S.I[4] = (float)sI[s][5]; S.I[5] = (float)sI[s][8];
+      S.mass = (real)L.mass; for (int k = 0; k < 3; k++) S.com[k] = (real)sc[s][k];
+      S.I[0] = (real)sI[s][0]; S.I[1] = (real)sI[s][1]; S.I[2] = (real)sI[s][2]; S.I[3] = (real)sI[s][4]; S.I[4] = (real)sI[s][5]; S.I[5] = (real)sI[s][8];
     }
     for (int k = 0; k < 3; k++) c[k] /= M;
     double I[9] = {0};
@@ -129,15 +129,15 @@ int build_model(int env_type_full, DevModel* m) {
       double rr = r[0] * r[0] + r[1] * r[1] + r[2] * r[2];
       for (int a = 0; a < 3; a++) for (int b = 0; b < 3; b++) I[3 * a + b] += sI[s][3 * a + b] + ms * ((a == b ? rr : 0.0) - r[a] * r[b]);
     }
-    m->mass[d] = (float)M; for (int k = 0; k < 3; k++) m->com[d][k] = (float)c[k];
-    m->I[d][0] = (float)I[0]; m->I[d][1] = (float)I[1]; m->I[d][2] = (float)I[2]; m->I[d][3] = (float)I[4]; m->I[d][4] = (float)I[5]; m->I[d][5] = (float)I[8];
+    m->mass[d] = (real)M; for (int k = 0; k < 3; k++) m->com[d][k] = (real)c[k];
+    m->I[d][0] = (real)I[0]; m->I[d][1] = (real)I[1]; m->I[d][2] = (real)I[2]; m->I[d][3] = (real)I[4]; m->I[d][4] = (real)I[5]; m->I[d][5] = (real)I[8];
   }
   const int aabb_links[2] = {11, 16};
-  for (int t = 0; t < 2; t++) for (int k = 0; k < 3; k++) { m->aabb_c[t][k] = (float)URG_LINKS[aabb_links[t]].aabb_center[k]; m->aabb_h[t][k] = (float)URG_LINKS[aabb_links[t]].aabb_half[k]; }
+  for (int t = 0; t < 2; t++) for (int k = 0; k < 3; k++) { m->aabb_c[t][k] = (real)URG_LINKS[aabb_links[t]].aabb_center[k]; m->aabb_h[t][k] = (real)URG_LINKS[aabb_links[t]].aabb_half[k]; }
 
   // ---- scene (same shape and pair order as the oracle's make_scene; the order is part of the spec because the
   // contact cap keeps the first UG_MAXC manifold points)
-  m->env_type = env_type_full; m->gravity = -9.8f;
+  m->env_type = env_type_full; m->gravity = (real)-9.8;
   int ns = 0;
   for (int k = 0; k < 17; k++) {
     int li = LINK_ORDER[k]; const UrgLinkModel& L = URG_LINKS[li];
@@ -146,38 +146,44 @@ int build_model(int env_type_full, DevModel* m) {
     D3 c = mv(lrot[li], bc); DM R = mm(lrot[li], br);
     double lc[3] = {lpos[li].v[0] + c.v[0], lpos[li].v[1] + c.v[1], lpos[li].v[2] + c.v[2]};
     DevShape s = mk_box(0, li, lc, L.box_half, 0.5);
-    for (int i = 0; i < 9; i++) s.lR[i] = (float)R.m[i];
+    for (int i = 0; i < 9; i++) s.lR[i] = (real)R.m[i];
     s.rbody = carrier[li];
     m->shapes[ns++] = s;
   }
   const double table_c[3] = {0, 0, -0.25}, table_h[3] = {0.5, 1.0, 0.25}, zero[3] = {0, 0, 0};
+  // plane.urdf at z = -0.5 under the table (env_ball_balance_v0.py:70, env_cubes_push_v0.py:77, env_golf_v0.py:77): 30 x 30 x 10
+  // box collider 5 m below its origin, lateral friction 1 [recalled]; static id 2
+  const double ground_c[3] = {0, 0, -0.5 - 5.0}, ground_h[3] = {15, 15, 5};
   const double paddle_h[3] = {0.05, 0.1, 0.005}, cube_h[3] = {0.02, 0.02, 0.02};
   switch (env_type) {
     case 0:
       m->nfree = 2; m->obs_dim = 6; m->act_dim = 3; m->max_steps = 500;
-      m->fmass[0] = 0.1f; box_inertia(0.1, paddle_h, m->finertia[0]);
-      m->fmass[1] = 0.01f; for (int k = 0; k < 3; k++) m->finertia[1][k] = (float)(0.4 * 0.01 * 0.02 * 0.02);
+      m->fmass[0] = (real)0.1; box_inertia(0.1, paddle_h, m->finertia[0]);
+      m->fmass[1] = (real)0.01; for (int k = 0; k < 3; k++) m->finertia[1][k] = (real)(0.4 * 0.01 * 0.02 * 0.02);
       m->shapes[ns++] = mk_box(1, -1, zero, paddle_h, 0.5);
       m->shapes[ns++] = mk_sphere(2, -1, 0.02, 0.5);
       m->shapes[ns++] = mk_box(-1, 0, table_c, table_h, 0.5);
+      m->shapes[ns++] = mk_box(-1, 2, ground_c, ground_h, 1.0);
       break;
     case 1:
       m->nfree = 3; m->obs_dim = 9; m->act_dim = 3; m->max_steps = 500;
-      m->fmass[0] = 0.1f; box_inertia(0.1, paddle_h, m->finertia[0]);
-      for (int b = 1; b < 3; b++) { m->fmass[b] = 0.01f; for (int k = 0; k < 3; k++) m->finertia[b][k] = (float)(0.4 * 0.01 * 0.003 * 0.003); }
+      m->fmass[0] = (real)0.1; box_inertia(0.1, paddle_h, m->finertia[0]);
+      for (int b = 1; b < 3; b++) { m->fmass[b] = (real)0.01; for (int k = 0; k < 3; k++) m->finertia[b][k] = (real)(0.4 * 0.01 * 0.003 * 0.003); }
       m->shapes[ns++] = mk_box(1, -1, zero, paddle_h, 0.5);
       m->shapes[ns++] = mk_sphere(2, -1, 0.003, 0.5);
       m->shapes[ns++] = mk_sphere(3, -1, 0.003, 0.5);
       m->shapes[ns++] = mk_box(-1, 0, table_c, table_h, 0.5);
+      m->shapes[ns++] = mk_box(-1, 2, ground_c, ground_h, 1.0);
       break;
     case 2:
       m->nfree = 2; m->obs_dim = 9; m->act_dim = 3; m->max_steps = 50;
-      for (int b = 0; b < 2; b++) { m->fmass[b] = 1.0f; box_inertia(1.0, cube_h, m->finertia[b]); m->shapes[ns++] = mk_box(b + 1, -1, zero, cube_h, 1.0); }
+      for (int b = 0; b < 2; b++) { m->fmass[b] = (real)1.0; box_inertia(1.0, cube_h, m->finertia[b]); m->shapes[ns++] = mk_box(b + 1, -1, zero, cube_h, 1.0); }
       m->shapes[ns++] = mk_box(-1, 0, table_c, table_h, 0.5);
+      m->shapes[ns++] = mk_box(-1, 2, ground_c, ground_h, 1.0);
       break;
     case 3: {
-      m->nfree = 1; m->obs_dim = 17; m->act_dim = 9; m->max_steps = 20; m->gravity = -10.0f;
-      m->fmass[0] = 1.0f; box_inertia(1.0, cube_h, m->finertia[0]);
+      m->nfree = 1; m->obs_dim = 17; m->act_dim = 9; m->max_steps = 20; m->gravity = (real)-10.0;
+      m->fmass[0] = (real)1.0; box_inertia(1.0, cube_h, m->finertia[0]);
       m->shapes[ns++] = mk_box(1, -1, zero, cube_h, 1.0);
       const double pc[3] = {0, 0, -5.0}, ph[3] = {15, 15, 5};
       m->shapes[ns++] = mk_box(-1, 0, pc, ph, 1.0);
@@ -187,12 +193,12 @@ int build_model(int env_type_full, DevModel* m) {
       m->nfree = 2; m->obs_dim = 9; m->act_dim = 3; m->max_steps = 100;
       double zc = UGP_CLUB_ZC;
       const double bh[3] = {0.015, 0.015, 0.075}, th[3] = {0.05, 0.015, 0.015}, dh[3] = {0.04, 0.04, 0.005};
-      float ib[3], it[3]; box_inertia(1.0, bh, ib); box_inertia(1.0, th, it);
+      real ib[3], it[3]; box_inertia(1.0, bh, ib); box_inertia(1.0, th, it);
       double idx = 1.0 / 12 * 0.01 * 0.01 + 0.25 * 0.04 * 0.04, idz = 0.5 * 0.04 * 0.04;
       double d0 = 0 - zc, d1 = -0.09 - zc, d2 = 0.08 - zc, pa = d0 * d0 + d1 * d1 + d2 * d2;
-      m->fmass[0] = 3.0f;
-      m->finertia[0][0] = (float)((double)ib[0] + it[0] + idx + pa); m->finertia[0][1] = (float)((double)ib[1] + it[1] + idx + pa); m->finertia[0][2] = (float)((double)ib[2] + it[2] + idz);
-      m->fmass[1] = 0.01f; for (int k = 0; k < 3; k++) m->finertia[1][k] = (float)(0.4 * 0.01 * 0.015 * 0.015);
+      m->fmass[0] = (real)3.0;
+      m->finertia[0][0] = (real)((double)ib[0] + it[0] + idx + pa); m->finertia[0][1] = (real)((double)ib[1] + it[1] + idx + pa); m->finertia[0][2] = (real)((double)ib[2] + it[2] + idz);
+      m->fmass[1] = (real)0.01; for (int k = 0; k < 3; k++) m->finertia[1][k] = (real)(0.4 * 0.01 * 0.015 * 0.015);
       const double c0[3] = {0, 0, d0}, c1[3] = {0, 0, d1}, c2[3] = {0, 0, d2};
       m->shapes[ns++] = mk_box(1, -1, c0, bh, 10.0, 0.1);
       m->shapes[ns++] = mk_box(1, 0, c1, th, 0.5);
@@ -201,6 +207,7 @@ int build_model(int env_type_full, DevModel* m) {
       m->shapes[ns++] = mk_box(-1, 0, table_c, table_h, 0.5);
       const double pc[3] = {0, -0.6, 0.02};
       m->shapes[ns++] = mk_box(-1, 1, pc, URG_PITCH_HALF, 0.5);
+      m->shapes[ns++] = mk_box(-1, 2, ground_c, ground_h, 1.0);
       break;
     }
   }
@@ -214,5 +221,20 @@ int build_model(int env_type_full, DevModel* m) {
   for (int a = 0; a < ns; a++) for (int b = 0; b < ns; b++) if (m->shapes[a].body == 0 && m->shapes[b].body < 0) add(a, b);
   if (np > UG_MAXPAIRS) return -1;
   m->npairs = np;
+  // Broad-phase bound per pair. The narrowphase reports a box-box manifold when the separating-axis slack is <= margin on
+  // all 15 axes, which can hold at a true distance above the margin, so the bounding spheres alone are not a safe cull.
+  // With A's three face axes a_i: |dc . a_i| <= hA_i + pB_i + margin, pB_i = sum_j hB_j |b_j . a_i|, |pB| <= sqrt(3) rB
+  // (Cauchy-Schwarz), hence |dc| <= rA + sqrt(3) rB + sqrt(3) margin, and the same with A and B exchanged. Against a static
+  // (world-aligned) box the vector from the box to A's centre obeys |e| <= sqrt(3) (rA + margin). Spheres have exact distances.
+  const double r3 = std::sqrt(3.0);
+  for (int p = 0; p < np; p++) {
+    const DevShape& A = m->shapes[m->pairs[p][0]]; const DevShape& B = m->shapes[m->pairs[p][1]];
+    const double mg = std::fmin((double)A.cbt, (double)B.cbt), ra = A.brad, rb = B.brad;
+    double bound;
+    if (B.body < 0) bound = A.kind == 1 ? ra + mg : r3 * (ra + mg);
+    else if (A.kind == 1 || B.kind == 1) bound = ra + rb + mg;
+    else bound = ra + rb + (r3 - 1.0) * std::fmin(ra, rb) + r3 * mg;
+    m->cullr[p] = (real)(bound * (1.0 + 1e-6));  // a hair of slack: the device evaluates the distance in `real`
+  }
   return 0;
 }
