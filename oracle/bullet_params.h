@@ -56,6 +56,8 @@ struct BulletParams {
   double cube_mass = 1.0;       // cube.urdf mass under globalScaling=0.04 [recalled: mass not scaled]
   double friction_cone = 1.0;   // 1: implicit cone over the two tangent rows; 0: independent box limits per row
   double roll_points = 1.0;     // rolling-friction rows on the first `roll_points` points of a manifold
+  double hull_links = 1.0;      // 1: gripper links with mesh geometry collide as convex polytopes; 0: as their fitted boxes (round 1)
+  double disc_half = 0.04;      // ablation: half side of the box standing in for the club's top disc
   double link_mask = 524287.0;  // ablation: bit i = robot link i collides (all 19 by default)
   double box_shrink = 0.0;      // ablation: metres taken off every half extent of the fitted robot link boxes
 };

@@ -7,6 +7,7 @@
 // the separation is below the pair's contact-breaking threshold (so "touching" is slightly fatter than penetration,
 // SURVEY.md §8a row A8). Stateless: contacts are a pure function of the poses.
 #pragma once
+#include "model_data.h"
 #include "urgo_math.h"
 
 namespace urgo {
@@ -171,6 +172,169 @@ inline bool sphere_box(V3 sc, double r, const BoxW& B, double margin, V3& on_box
   on_box = B.c + B.R * cl;
   n_box_to_sphere = B.R * nl;
   return true;
+}
+
+
+// ----------------------------------------------------------------------------------------------------------------
+// Convex polytope (a gripper link whose URDF collision geometry is a mesh: Bullet collides the convex hull of the mesh
+// vertices [recalled: BulletUrdfImporter]) against a box or a sphere. Separating-axis test over the polytope's face
+// normals, the box's face normals and the cross products of their edge directions, then clipping of the incident face
+// against the side planes of the reference face: the published polyhedral contact-clipping scheme (Bullet's
+// btPolyhedralContactClipping / ODE's box-box generalised to face lists), with the same acceptance rule as box_box
+// above (points within `margin` of the reference face are kept, at most four, spread from the deepest).
+struct PolyW { int nv, nf, ne; V3 v[URG_POLY_MAXV]; V3 fn[URG_POLY_MAXF]; double fd[URG_POLY_MAXF]; V3 ed[URG_POLY_MAXE]; const UrgPoly* src; };
+
+inline PolyW poly_world(const UrgPoly& P, V3 origin, const M3& R) {
+  PolyW w; w.nv = P.nv; w.nf = P.nf; w.ne = P.ne; w.src = &P;
+  for (int i = 0; i < P.nv; i++) w.v[i] = origin + R * V3(P.v[i][0], P.v[i][1], P.v[i][2]);
+  for (int f = 0; f < P.nf; f++) { w.fn[f] = R * V3(P.fn[f][0], P.fn[f][1], P.fn[f][2]); w.fd[f] = P.fn[f][3] + dot(w.fn[f], origin); }
+  for (int e = 0; e < P.ne; e++) w.ed[e] = R * V3(P.ed[e][0], P.ed[e][1], P.ed[e][2]);
+  return w;
+}
+
+// Clips the convex polygon `poly` (n <= 16 vertices) against the half-space m . (p - o) >= 0.
+inline int clip_halfspace(V3* poly, int n, V3 o, V3 m) {
+  V3 out[24]; int k = 0;
+  for (int i = 0; i < n; i++) {
+    V3 P = poly[i], Q = poly[(i + 1) % n];
+    double dp = dot(m, P - o), dq = dot(m, Q - o);
+    if (dp >= 0) out[k++] = P;
+    if ((dp >= 0) != (dq >= 0)) { double t = dp / (dp - dq); out[k++] = P + (Q - P) * t; }
+  }
+  if (k > 16) k = 16;
+  for (int i = 0; i < k; i++) poly[i] = out[i];
+  return k;
+}
+
+inline int keep_four(const V3* pts, const double* dist, int m, int* sel) {
+  if (m <= 4) { for (int j = 0; j < m; j++) sel[j] = j; return m; }
+  int i0 = 0;
+  for (int v = 1; v < m; v++) if (-dist[v] > -dist[i0]) i0 = v;   // deepest first
+  for (int j = 0; j < 4; j++) sel[j] = (i0 + (j * m) / 4) % m;
+  return 4;
+}
+
+// A = polytope (world), B = box. Normal n of the output points from B to A, posA = posB + n * dist.
+inline int poly_box(const PolyW& A, const BoxW& B, double margin, CPoint out[4]) {
+  V3 bax[3] = {B.R.col(0), B.R.col(1), B.R.col(2)};
+  double best = -1e300; int kind = 0, idx = 0, sgn = 1; V3 nBA;  // kind 0: face of A, 1: face of B (idx axis, sgn side), 2: edge pair
+  for (int f = 0; f < A.nf; f++) {                 // faces of A: lowest point of B above the face plane
+    const V3 n = A.fn[f];
+    double sB = dot(n, B.c) - (B.h.x * std::fabs(dot(n, bax[0])) + B.h.y * std::fabs(dot(n, bax[1])) + B.h.z * std::fabs(dot(n, bax[2])));
+    double s = sB - A.fd[f];
+    note_decision(s - margin);
+    if (s > margin) return 0;
+    if (s > best) { best = s; kind = 0; idx = f; nBA = -n; }
+  }
+  double lo[3], hi[3];
+  for (int j = 0; j < 3; j++) {                    // faces of B: extent of A along the box axis, relative to the box centre
+    lo[j] = 1e300; hi[j] = -1e300;
+    for (int i = 0; i < A.nv; i++) { double p = dot(bax[j], A.v[i] - B.c); lo[j] = std::fmin(lo[j], p); hi[j] = std::fmax(hi[j], p); }
+    double sp = lo[j] - B.h[j], sm = -hi[j] - B.h[j];   // A beyond the +j face / beyond the -j face
+    note_decision(sp - margin); note_decision(sm - margin);
+    if (sp > margin || sm > margin) return 0;
+    if (sp > best) { best = sp; kind = 1; idx = j; sgn = 1; nBA = bax[j]; }
+    if (sm > best) { best = sm; kind = 1; idx = j; sgn = -1; nBA = -bax[j]; }
+  }
+  int ea = 0, eb = 0;
+  for (int e = 0; e < A.ne; e++)
+    for (int j = 0; j < 3; j++) {                  // edge x edge
+      V3 L = cross(A.ed[e], bax[j]); double l = norm(L);
+      if (l <= 1e-9) continue;
+      L = L * (1.0 / l);
+      double mnA = 1e300, mxA = -1e300;
+      for (int i = 0; i < A.nv; i++) { double p = dot(L, A.v[i] - B.c); mnA = std::fmin(mnA, p); mxA = std::fmax(mxA, p); }
+      double rB = B.h.x * std::fabs(dot(L, bax[0])) + B.h.y * std::fabs(dot(L, bax[1])) + B.h.z * std::fabs(dot(L, bax[2]));
+      double s1 = mnA - rB, s2 = -mxA - rB;        // A on the +L side of B / on the -L side
+      double sx = std::fmax(s1, s2);
+      note_decision(sx - margin);
+      if (sx > margin) return 0;
+      if (edge_bias(sx) > best) { best = sx; kind = 2; ea = e; eb = j; nBA = s1 >= s2 ? L : -L; }
+    }
+  if (kind == 2) {                                 // one point: closest points of the two supporting edges
+    // supporting feature of each body towards the other: mean of the vertices within 10 um of the extreme
+    double exA = 1e300; for (int i = 0; i < A.nv; i++) exA = std::fmin(exA, dot(nBA, A.v[i]));
+    V3 pa; int ca = 0; for (int i = 0; i < A.nv; i++) if (dot(nBA, A.v[i]) <= exA + 1e-5) { pa += A.v[i]; ca++; }
+    pa = pa * (1.0 / ca);
+    V3 pb = B.c;
+    for (int k = 0; k < 3; k++) if (k != eb) pb += bax[k] * ((dot(nBA, bax[k]) > 0 ? 1.0 : -1.0) * B.h[k]);
+    V3 ua = A.ed[ea], ub = bax[eb], d = pb - pa;
+    double uaub = dot(ua, ub), q1 = dot(ua, d), q2 = -dot(ub, d), den = 1.0 - uaub * uaub, beta = 0;
+    if (den > 1e-4) beta = (uaub * q1 + q2) / den;
+    pb += ub * beta;
+    out[0].n = nBA; out[0].dist = best; out[0].posB = pb; out[0].posA = pb + nBA * best;
+    return 1;
+  }
+  V3 poly[24]; int n = 0; V3 rn; double rd;         // reference plane rn . p = rd (outward)
+  if (kind == 0) {                                 // reference face on A; incident = the box face most against it
+    rn = A.fn[idx]; rd = A.fd[idx];
+    int la = 0; double lav = -1; for (int j = 0; j < 3; j++) { double v = std::fabs(dot(rn, bax[j])); if (v > lav) { lav = v; la = j; } }
+    int a1 = (la + 1) % 3, a2 = (la + 2) % 3;
+    double sg = dot(rn, bax[la]) > 0 ? -1.0 : 1.0;
+    V3 fc = B.c + bax[la] * (sg * B.h[la]), e1 = bax[a1] * B.h[a1], e2 = bax[a2] * B.h[a2];
+    poly[0] = fc - e1 - e2; poly[1] = fc + e1 - e2; poly[2] = fc + e1 + e2; poly[3] = fc - e1 + e2; n = 4;
+    const int cnt = A.src->fcount[idx]; const int* loop = A.src->floop[idx];
+    for (int k = 0; k < cnt && n > 0; k++) {
+      V3 o = A.v[loop[k]], e = A.v[loop[(k + 1) % cnt]] - o;
+      n = clip_halfspace(poly, n, o, cross(rn, e));
+    }
+  } else {                                         // reference face on B; incident = A's face most against it
+    rn = bax[idx] * (double)sgn; rd = dot(rn, B.c) + B.h[idx];
+    int fi = 0; double fv = 1e300; for (int f = 0; f < A.nf; f++) { double v = dot(A.fn[f], rn); if (v < fv) { fv = v; fi = f; } }
+    const int cnt = A.src->fcount[fi]; const int* loop = A.src->floop[fi];
+    for (int k = 0; k < cnt; k++) poly[n++] = A.v[loop[k]];
+    int c1 = (idx + 1) % 3, c2 = (idx + 2) % 3;
+    for (int t = 0; t < 4 && n > 0; t++) {
+      V3 ax = bax[t < 2 ? c1 : c2] * ((t & 1) ? -1.0 : 1.0);     // keep ax . (p - c) <= h
+      n = clip_halfspace(poly, n, B.c + ax * B.h[t < 2 ? c1 : c2], -ax);
+    }
+  }
+  V3 kept[16]; double dist[16]; int m = 0;
+  for (int i = 0; i < n; i++) {
+    double dv = dot(rn, poly[i]) - rd;              // signed distance above the reference face
+    note_decision(margin - dv);
+    if (dv <= margin) { kept[m] = poly[i]; dist[m] = dv; m++; }
+  }
+  if (m == 0) return 0;
+  int sel[4]; int cnt = keep_four(kept, dist, m, sel);
+  for (int j = 0; j < cnt; j++) {
+    V3 pt = kept[sel[j]]; double dv = dist[sel[j]];
+    out[j].n = nBA; out[j].dist = dv;
+    if (kind == 0) { out[j].posB = pt; out[j].posA = pt + nBA * dv; }     // the point is on B (incident), A's face is the reference
+    else { out[j].posA = pt; out[j].posB = pt - nBA * dv; }
+  }
+  return cnt;
+}
+
+// Closest point of the polytope to a sphere centre: returns like sphere_box (point on the polytope, normal towards the sphere).
+inline bool sphere_poly(V3 sc, double r, const PolyW& A, double margin, V3& on_poly, V3& n_to_sphere, double& dist) {
+  double mx = -1e300; int fm = 0;
+  for (int f = 0; f < A.nf; f++) { double s = dot(A.fn[f], sc) - A.fd[f]; if (s > mx) { mx = s; fm = f; } }
+  if (mx <= 0) {  // centre inside: out through the nearest face
+    n_to_sphere = A.fn[fm]; on_poly = sc - A.fn[fm] * mx; dist = mx - r;
+  } else {
+    double bd = 1e300; V3 bp;
+    for (int f = 0; f < A.nf; f++) {
+      double s = dot(A.fn[f], sc) - A.fd[f];
+      if (s <= 0) continue;
+      V3 q = sc - A.fn[f] * s;                       // projection on the face plane
+      const int cnt = A.src->fcount[f]; const int* loop = A.src->floop[f];
+      bool inside = true; double be = 1e300; V3 bq;
+      for (int k = 0; k < cnt; k++) {
+        V3 o = A.v[loop[k]], e = A.v[loop[(k + 1) % cnt]] - o;
+        if (dot(cross(A.fn[f], e), q - o) < 0) inside = false;
+        double t = dot(sc - o, e) / dot(e, e); t = std::fmin(1.0, std::fmax(0.0, t));
+        V3 c = o + e * t; double d2 = dot(sc - c, sc - c);
+        if (d2 < be) { be = d2; bq = c; }
+      }
+      V3 cp = inside ? q : bq; double d2 = inside ? s * s : be;
+      if (d2 < bd) { bd = d2; bp = cp; }
+    }
+    double len = std::sqrt(bd);
+    on_poly = bp; n_to_sphere = (sc - bp) * (1.0 / len); dist = len - r;
+  }
+  note_decision(dist - margin);
+  return dist < margin;
 }
 
 }  // namespace urgo

@@ -34,7 +34,8 @@ static const double GEAR_RATIO[5] = {1.0, -1.0, -1.0, 1.0, -1.0};
 static const int LINK_ORDER[17] = {12, 17, 11, 16, 10, 15, 9, 14, 13, 18, 8, 6, 5, 4, 3, 2, 1};
 
 struct ShapeDef {
-  int kind;   // 0 box, 1 sphere
+  int kind;   // 0 box, 1 sphere, 2 convex polytope (poly = index into URG_POLYS, in the frame of robot link `link`)
+  int poly = -1;
   int body;   // 0 robot, 1..3 free body index+1, -1 static
   int link;   // robot link index, or sub-shape id on a free body
   V3 lc; M3 lR; V3 half; double radius;
@@ -74,7 +75,8 @@ inline Scene make_scene(int env_type_full) {
     ShapeDef s = mk_box(0, LINK_ORDER[k], V3(L.box_center[0], L.box_center[1], L.box_center[2]),
                         V3(L.box_half[0], L.box_half[1], L.box_half[2]), bp().robot_mu);
     for (int i = 0; i < 9; i++) s.lR.m[i] = L.box_rot[i];
-    if (!(((long)bp().link_mask >> LINK_ORDER[k]) & 1)) s.half = V3(1e-6, 1e-6, 1e-6);  // ablation: link does not collide
+    if (bp().hull_links != 0.0 && URG_LINK_POLY[LINK_ORDER[k]] >= 0) { s.kind = 2; s.poly = URG_LINK_POLY[LINK_ORDER[k]]; }
+    if (!(((long)bp().link_mask >> LINK_ORDER[k]) & 1)) { s.half = V3(1e-6, 1e-6, 1e-6); s.kind = 0; }  // ablation: link does not collide
     else if (bp().box_shrink > 0 && LINK_ORDER[k] != 12 && LINK_ORDER[k] != 17) s.half = V3(std::fmax(s.half.x - bp().box_shrink, 1e-4), std::fmax(s.half.y - bp().box_shrink, 1e-4), std::fmax(s.half.z - bp().box_shrink, 1e-4));
     sc.shapes.push_back(s);
   }
@@ -130,7 +132,7 @@ inline Scene make_scene(int env_type_full) {
       sc.fmass[1] = 0.01; sc.finertia[1] = V3(1, 1, 1) * (0.4 * 0.01 * 0.015 * 0.015);
       sc.shapes.push_back(mk_box(1, -1, V3(0, 0, d0), V3(0.015, 0.015, 0.075), 10.0, 0.1));
       sc.shapes.push_back(mk_box(1, 0, V3(0, 0, d1), V3(0.05, 0.015, 0.015), bm));
-      sc.shapes.push_back(mk_box(1, 1, V3(0, 0, d2), V3(0.04, 0.04, 0.005), bm));  // disc r=0.04 h=0.01 as a box
+      sc.shapes.push_back(mk_box(1, 1, V3(0, 0, d2), V3(bp().disc_half, bp().disc_half, 0.005), bm));  // disc r=0.04 h=0.01 as a box
       sc.shapes.push_back(mk_sphere(2, -1, 0.015, bm, 0.1, 10.0));
       sc.shapes.push_back(mk_box(-1, 0, table_c, table_h, bm));
       sc.shapes.push_back(mk_box(-1, 1, V3(0, -0.6, 0.02), V3(URG_PITCH_HALF[0], URG_PITCH_HALF[1], URG_PITCH_HALF[2]), bm));
@@ -333,7 +335,20 @@ struct World {
       double margin = std::fmin(A.cbt, B.cbt);
       CPoint pts[4]; int n = 0;
       BoxW a = world_box(A), b = world_box(B);
-      if (A.kind == 0 && B.kind == 0) {
+      if (A.kind == 2) {   // robot link with mesh geometry against a box or a sphere
+        // mid-phase: the link's bounding box (which contains the polytope) with the same margin; only then the polytope
+        bool close;
+        if (B.kind == 0) close = box_box(a, b, margin, pts) > 0;
+        else { V3 oa, na; double d; close = sphere_box(b.c, B.radius, a, margin, oa, na, d); }
+        if (close) {
+          PolyW pa = poly_world(URG_POLYS[A.poly], rob.p[A.link], rob.R[A.link]);
+          if (B.kind == 0) n = poly_box(pa, b, margin, pts);
+          else {
+            V3 oa, na; double d;
+            if (sphere_poly(b.c, B.radius, pa, margin, oa, na, d)) { pts[0].n = -na; pts[0].dist = d; pts[0].posA = oa; pts[0].posB = oa + na * d; n = 1; }
+          }
+        }
+      } else if (A.kind == 0 && B.kind == 0) {
         n = box_box(a, b, margin, pts);
       } else if (A.kind == 1 && B.kind == 0) {
         V3 ob, nb; double d;

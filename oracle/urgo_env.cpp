@@ -517,7 +517,7 @@ int urgo_set_param(const char* name, double v) {
 #define URGO_P(f) if (n == #f) { P.f = v; return 0; }
   URGO_P(erp) URGO_P(erp2) URGO_P(linear_slop) URGO_P(restitution_threshold) URGO_P(lin_damping) URGO_P(ang_damping) URGO_P(contact_breaking)
   URGO_P(motor_kp) URGO_P(motor_kd) URGO_P(ik_damping) URGO_P(max_friction) URGO_P(solver_iters) URGO_P(robot_mu) URGO_P(body_mu) URGO_P(cube_mu)
-  URGO_P(plane_mu) URGO_P(cube_mass) URGO_P(friction_cone) URGO_P(roll_points) URGO_P(link_mask) URGO_P(box_shrink)
+  URGO_P(plane_mu) URGO_P(cube_mass) URGO_P(friction_cone) URGO_P(roll_points) URGO_P(link_mask) URGO_P(box_shrink) URGO_P(hull_links) URGO_P(disc_half)
 #undef URGO_P
   return -1;
 }

@@ -167,7 +167,7 @@ def test_urand_is_24_bit_uniform_and_keyed():
     assert L.urgo_urand(7, 3, 1, 0) != L.urgo_urand(8, 3, 1, 0) != L.urgo_urand(7, 3, 2, 0)
 
 
-RESET_TICKS = {'BallBalance': (194, 194), 'TwoBallsBalance': (194, 194), 'CubesPush': (130, 150), 'CubesGrasp': (11, 11), 'Golf': (175, 190)}
+RESET_TICKS = {'BallBalance': (170, 180), 'TwoBallsBalance': (170, 180), 'CubesPush': (130, 155), 'CubesGrasp': (11, 11), 'Golf': (180, 192)}
 
 
 @pytest.mark.parametrize('name', ENVS)
@@ -251,3 +251,22 @@ def test_autoreset_returns_first_observation_of_next_episode():
     assert not np.allclose(last['final_obs'], last['obs'])
     nxt = ob.step(a, u=np.array([0.2, 0.2]), autoreset=True)
     assert not nxt['truncated'].any()
+
+
+def test_scripted_grasp_reaches_every_sub_goal_through_the_physics():
+    """approach -> close -> raise on CubesGrasp (tests/scripted_grasp.py): +5 approached, +5 grasped, +10 raised with is_success,
+    none of which a random policy ever sees (env_cubes_grasp_v0.py:150-168, 206-233)."""
+    import scripted_grasp as G
+    n = 4
+    ob = O.OracleBatch('CubesGrasp', n, seed=11)
+    ob.reset()
+    log = G.run(ob, n)
+    bits = np.array([r['obs'][:, :2] for _, r in log])            # [step, env, (approached, grasped)]
+    rew = np.array([r['reward'] for _, r in log])
+    assert (bits[0] == 0).all() and (bits[-1] == 1).all()
+    first_app = (bits[:, :, 0] == 1).argmax(0); first_grasp = (bits[:, :, 1] == 1).argmax(0)
+    assert (first_app == 2).all() and (first_grasp == 3).all()     # down-around-the-cube step, then the closing step
+    assert np.allclose(rew[2], 5.15, atol=0.1) and np.allclose(rew[3], 4.9, atol=1e-9)
+    last = log[-1][1]
+    assert last['terminated'].all() and last['success'].all() and np.allclose(last['reward'], 9.9) and (last['obs'][:, 12] > 0.2).all()
+    assert len(log) <= 20                                          # inside the env's 20-step TimeLimit

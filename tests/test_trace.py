@@ -11,7 +11,7 @@ def test_trace_round_trip_and_exact_replay(built, tmp_path):
     a = O.OracleBatch('CubesPush', 3, seed=4); a.reset()
     actions = rng.uniform(-0.1, 0.1, (4, 3, 3)).astype(np.float32)
     tr = T.record(a, 'CubesPush', actions)
-    assert tr['obs'].shape == (4, 3, 9) and tr['state'].shape == (4, 3, 96) and tr['pairs'].shape == (4, 3, 16, 2)
+    assert tr['obs'].shape == (4, 3, 9) and tr['state'].shape == (4, 3, 96) and tr['pairs'].shape == (4, 3, 64, 2)
     path = str(tmp_path / 'push.npz')
     T.save(path, tr)
     back = T.load(path)

@@ -96,6 +96,80 @@ def min_volume_box(pts):
     return R @ cb, R, half
 
 
+POLY_LINKS = (8, 9, 10, 11, 13, 14, 15, 16, 18)   # gripper links with mesh collision geometry (pads 12 / 17 are boxes)
+POLY_MAXV, POLY_MAXF, POLY_MAXL, POLY_MAXE = 16, 32, 8, 12
+
+
+def reduce_hull(pts, kmax=POLY_MAXV):
+    """Inner approximation of the convex hull of `pts` by at most kmax of its own vertices: start from the six axis
+    extremes, then keep adding the hull vertex farthest outside the current polytope. Being a subset of the hull it never
+    protrudes beyond the true geometry (a pad must stay proud of the finger that carries it). Returns (vertices, max
+    distance of a dropped hull vertex to the polytope)."""
+    from scipy.spatial import ConvexHull
+    H0 = ConvexHull(pts)
+    V = pts[H0.vertices]
+    sel = []
+    for ax in range(3):
+        for sg in (1, -1):
+            i = int(np.argmax(sg * V[:, ax]))
+            if i not in sel:
+                sel.append(i)
+    while True:
+        H = ConvexHull(V[sel])
+        d = (H.equations[:, :3] @ V.T + H.equations[:, 3:4]).max(0)
+        d[sel] = -1
+        i = int(np.argmax(d))
+        if len(sel) >= kmax or d[i] < 1e-5:
+            return V[sel], float(max(d[i], 0.0))
+        sel.append(i)
+
+
+def polytope_features(P, ang_tol_deg=2.0, off_tol=2e-5):
+    """Faces (outward unit normal, offset, CCW vertex loop; coplanar hull triangles merged), and the unique edge directions."""
+    from scipy.spatial import ConvexHull
+    H = ConvexHull(P)
+    n, d = H.equations[:, :3], -H.equations[:, 3]
+    used = np.zeros(len(n), bool)
+    ct = math.cos(math.radians(ang_tol_deg))
+    faces = []
+    for i in range(len(n)):
+        if used[i]:
+            continue
+        grp = [j for j in range(len(n)) if not used[j] and n[i] @ n[j] > ct and abs(d[i] - d[j]) < off_tol + 1e-3 * (1 - n[i] @ n[j])]
+        for j in grp:
+            used[j] = True
+        vs = sorted(set(int(v) for j in grp for v in H.simplices[j]))
+        nn = n[grp].mean(0)
+        nn /= np.linalg.norm(nn)
+        dd = float(max(P[vs] @ nn))
+        c = P[vs].mean(0)
+        u = np.cross(nn, [1, 0, 0]) if abs(nn[0]) < 0.9 else np.cross(nn, [0, 1, 0])
+        u /= np.linalg.norm(u)
+        w = np.cross(nn, u)
+        q = np.stack([(P[vs] - c) @ u, (P[vs] - c) @ w], 1)
+        if len(vs) > 3:
+            vs = [vs[k] for k in ConvexHull(q).vertices]        # CCW seen from outside
+        else:
+            ang = np.arctan2(q[:, 1], q[:, 0])
+            vs = [vs[k] for k in np.argsort(ang)]
+        faces.append((nn, dd, vs))
+    # Edge directions for the edge-edge separating axes: the POLY_MAXE longest, merging directions within 8 degrees. The
+    # vertex subset keeps many short edges around what were fillets of the mesh; their cross products with the partner's
+    # edges are near-duplicates of these. (A coarser candidate set can only miss a separating axis, i.e. report a shallow
+    # contact where the bodies are a hair apart.)
+    edges = {}
+    for nn, dd, vs in faces:
+        for a in range(len(vs)):
+            i, k = vs[a], vs[(a + 1) % len(vs)]
+            edges[(min(i, k), max(i, k))] = P[k] - P[i]
+    dirs = []
+    for e in sorted(edges.values(), key=lambda v: -np.linalg.norm(v)):
+        u = e / np.linalg.norm(e)
+        if len(dirs) < POLY_MAXE and not any(abs(u @ x) > math.cos(math.radians(8.0)) for x in dirs):
+            dirs.append(u)
+    return faces, dirs
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument('--ref', default='/root/reference')
@@ -103,6 +177,7 @@ def main():
     udir = os.path.join(args.ref, 'urgym', 'urdf')
     links_xml, order = parse_urdf(os.path.join(udir, 'ur5_robotiq_85.urdf'))
     table = []
+    mesh_pts = {}
     for idx, (name, j, parent) in enumerate(order):
         l = links_xml[name]
         o = j.find('origin')
@@ -134,12 +209,17 @@ def main():
         if geom.find('mesh') is not None:
             m = geom.find('mesh')
             sc = fvec(m.get('scale')) if m.get('scale') else [1, 1, 1]
-            pts = load_mesh(os.path.normpath(os.path.join(udir, m.get('filename')))) * np.array(sc) + np.array(cxyz)
+            raw = load_mesh(os.path.normpath(os.path.join(udir, m.get('filename'))))
+            if os.environ.get('URGYM_DAE_YUP') and m.get('filename').lower().endswith('.dae'):
+                raw = np.stack([raw[:, 0], -raw[:, 2], raw[:, 1]], 1)   # experiment: Y_UP -> Z_UP (+90 deg about x)
+            pts = raw * np.array(sc) + np.array(cxyz)
             lo, hi = pts.min(0), pts.max(0)
             aabb_c, aabb_h = (lo + hi) / 2, (hi - lo) / 2
             bc, bR, bh = min_volume_box(pts)
             inertia_h = aabb_h + 2 * HULL_MARGIN  # hull aabb incl. margin, plus the margin added once more (recalled)
             is_mesh = 1
+            if idx in POLY_LINKS:
+                mesh_pts[idx] = (m.get('filename'), pts)
         else:
             size = np.array(fvec(geom.find('box').get('size')))
             aabb_c, aabb_h = np.array(cxyz, dtype=float), size / 2
@@ -156,6 +236,17 @@ def main():
                           aabb_center=aabb_c.tolist(), aabb_half=aabb_h.tolist(),
                           box_center=bc.tolist(), box_rot=bR.reshape(-1).tolist(), box_half=bh.tolist(),
                           is_mesh=is_mesh))
+    polys, poly_of_file, link_poly = [], {}, [-1] * len(table)
+    for idx in POLY_LINKS:
+        fname, pts = mesh_pts[idx]
+        if fname not in poly_of_file:
+            P, err = reduce_hull(pts)
+            faces, dirs = polytope_features(P)
+            assert len(P) <= POLY_MAXV and len(faces) <= POLY_MAXF and len(dirs) <= POLY_MAXE and max(len(f[2]) for f in faces) <= POLY_MAXL, (fname, len(P), len(faces), len(dirs))
+            poly_of_file[fname] = len(polys)
+            polys.append(dict(mesh=os.path.basename(fname), verts=P.tolist(), faces=[dict(n=f[0].tolist(), d=f[1], loop=f[2]) for f in faces],
+                              edge_dirs=[e.tolist() for e in dirs], dropped_vertex_max_mm=err * 1000))
+        link_poly[idx] = poly_of_file[fname]
     names = [t['name'] for t in table]
     expect = ['base_link', 'shoulder_link', 'upper_arm_link', 'forearm_link', 'wrist_1_link', 'wrist_2_link',
               'wrist_3_link', 'ee_link', 'robotiq_arg2f_base_link', 'left_outer_knuckle', 'left_outer_finger',
@@ -164,7 +255,7 @@ def main():
     assert names == expect, names
     pitch = load_mesh(os.path.join(args.ref, 'urgym', 'meshes', 'golf_pitch.obj'))
     plo, phi = pitch.min(0), pitch.max(0)
-    model = dict(links=table, pitch_half=((phi - plo) / 2).tolist(), pitch_center=((phi + plo) / 2).tolist())
+    model = dict(links=table, pitch_half=((phi - plo) / 2).tolist(), pitch_center=((phi + plo) / 2).tolist(), polytopes=polys, link_polytope=link_poly)
 
     here = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
     os.makedirs(os.path.join(here, 'urgym_b200', 'model'), exist_ok=True)
@@ -197,6 +288,26 @@ def main():
             t['index'], t['name']))
     H.append('};')
     H.append('static const double URG_PITCH_HALF[3] = %s;' % arr(model['pitch_half']))
+    H.append('// Convex polytopes of the gripper links whose collision geometry is a mesh (Bullet: convex hull of the mesh vertices):')
+    H.append('// at most %d of the hull\'s own vertices (inner approximation), faces with outward normals and CCW loops, unique edge' % POLY_MAXV)
+    H.append('// directions. Link frame, URDF scale and collision origin applied. Left / right links share a mesh.')
+    H.append('#define URG_NPOLY %d' % len(polys))
+    H.append('#define URG_POLY_MAXV %d' % POLY_MAXV)
+    H.append('#define URG_POLY_MAXF %d' % POLY_MAXF)
+    H.append('#define URG_POLY_MAXL %d' % POLY_MAXL)
+    H.append('#define URG_POLY_MAXE %d' % POLY_MAXE)
+    H.append('struct UrgPoly { int nv, nf, ne; double v[URG_POLY_MAXV][3]; double fn[URG_POLY_MAXF][4]; int fcount[URG_POLY_MAXF]; int floop[URG_POLY_MAXF][URG_POLY_MAXL]; double ed[URG_POLY_MAXE][3]; };')
+    H.append('static const UrgPoly URG_POLYS[URG_NPOLY] = {')
+    for pl in polys:
+        vv = ', '.join(arr(v) for v in pl['verts'])
+        ff = ', '.join(arr(f['n'] + [f['d']]) for f in pl['faces'])
+        fc = ', '.join(str(len(f['loop'])) for f in pl['faces'])
+        fl = ', '.join('{' + ', '.join(str(i) for i in f['loop']) + '}' for f in pl['faces'])
+        ee = ', '.join(arr(e) for e in pl['edge_dirs'])
+        H.append('  { %d, %d, %d, {%s}, {%s}, {%s}, {%s}, {%s} },  // %s (dropped hull vertices within %.2f mm)' % (
+            len(pl['verts']), len(pl['faces']), len(pl['edge_dirs']), vv, ff, fc, fl, ee, pl['mesh'], pl['dropped_vertex_max_mm']))
+    H.append('};')
+    H.append('static const int URG_LINK_POLY[URG_NLINK] = {%s};' % ', '.join(str(x) for x in link_poly))
     H.append('')
     txt = '\n'.join(H)
     for rel in ('oracle/model_data.h', 'urgym_b200/csrc/model_data.h'):

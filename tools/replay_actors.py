@@ -8,8 +8,8 @@ also solve the task here: the only end-to-end pin of the rigid-body arithmetic a
     python tools/replay_actors.py [--episodes 1000] [--backend oracle|cuda] [--set name=value ...] [--out file.json] [env ...]
 
 --backend oracle: the fp64 CPU restatement, all host threads (--set overrides recalled parameters, oracle/bullet_params.h).
---backend cuda:   the CUDA library; the MLP runs in torch on the device and drives URGymVectorEnv-style stepping with no
-                  host synchronisation inside an episode.
+--backend cuda:   the CUDA library; the MLP runs in torch on the device and drives the batch with no host synchronisation
+                  on the step path (one `alive.any()` every 16 steps to stop early). cuda64 = the fp64 parity build.
 """
 import argparse
 import json
@@ -68,6 +68,8 @@ def rollout_cuda(name, episodes, seed=123, precision='f32'):
     ret = torch.zeros(episodes, dtype=torch.float64, device=dev); length = torch.zeros(episodes, dtype=torch.int64, device=dev)
     succ = torch.zeros(episodes, dtype=torch.bool, device=dev)
     for k in range(b.max_episode_steps):
+        if k % 16 == 15 and not bool(alive.any()):      # the only host synchronisation: once every 16 steps, to stop early
+            break
         a = act(obs)
         o, r, term, trunc, su = b.step(a, autoreset=False)
         obs = torch.where(alive[:, None], o, obs)

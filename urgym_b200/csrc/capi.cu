@@ -42,6 +42,7 @@ struct urgym_env_s {
   uint8_t *d_term = nullptr, *d_trunc = nullptr, *d_succ = nullptr, *d_mask = nullptr; int32_t* d_nticks = nullptr;
   uint8_t* d_defer = nullptr; bool split_reset = false;  // auto-reset in its own launch
   cudaStream_t own_stream = nullptr, last_stream = nullptr;
+  cudaEvent_t order_evt = nullptr; bool used = false;   // cross-stream ordering of successive calls on one handle
 };
 
 namespace {
@@ -73,7 +74,6 @@ int launch_env_g(urgym_handle h, const KParams& P, cudaStream_t st) {
   env_kernel<ENV, G><<<(h->N + EPB - 1) / EPB, 32, smem, st>>>(P);
   g_launches++;
   CK(cudaGetLastError());
-  h->last_stream = st;
   return URGYM_OK;
 }
 template <int ENV>
@@ -81,8 +81,20 @@ int launch_env(urgym_handle h, const KParams& P, cudaStream_t st) {
   return launch_env_g<ENV, 32>(h, P, st);
 }
 
+// Calls on one handle are ordered even when they arrive on different streams (the *_host entries work on the handle's own
+// stream, the device entries on the caller's): the new stream waits for the work the previous call enqueued.
+int order_after_last(urgym_handle h, cudaStream_t st) {
+  if (h->used && h->last_stream != st) {
+    CK(cudaEventRecord(h->order_evt, h->last_stream));
+    CK(cudaStreamWaitEvent(st, h->order_evt, 0));
+  }
+  h->used = true; h->last_stream = st;
+  return URGYM_OK;
+}
+
 int launch(urgym_handle h, KParams& P, void* stream) {
   CK(cudaSetDevice(h->device));
+  { int rc = order_after_last(h, (cudaStream_t)stream); if (rc) return rc; }
   P.model = h->dmodel; P.state = h->state; P.N = h->N; P.contacts = h->contacts; P.ccount = h->ccount; P.hitmask = h->hitmask; P.stats = h->stats;
   P.seed = h->seed; P.gidx0 = h->gidx0; P.sparse = h->sparse;
   cudaStream_t st = (cudaStream_t)stream;  // NULL = the legacy default stream, as in the CUDA runtime
@@ -154,6 +166,7 @@ int urgym_create(int env_type, int num_envs, int device, uint64_t seed, int env_
   CK(cudaMalloc(&h->d_nticks, n * 2 * sizeof(int32_t)));
   CK(cudaMalloc(&h->d_defer, n)); CK(cudaMemset(h->d_defer, 0, n));
   CK(cudaStreamCreateWithFlags(&h->own_stream, cudaStreamNonBlocking));
+  CK(cudaEventCreateWithFlags(&h->order_evt, cudaEventDisableTiming));
   std::vector<real> init(n * UG_STATE, 0._r);
   for (size_t i = 0; i < n; i++) { real* r = init.data() + i * UG_STATE; r[37] = 1._r; for (int b = 0; b < UG_MAXFREE; b++) r[38 + 13 * b + 6] = 1._r; }
   CK(cudaMemcpy(h->state, init.data(), init.size() * sizeof(real), cudaMemcpyHostToDevice));
@@ -168,6 +181,7 @@ int urgym_destroy(urgym_handle h) {
   void* ptrs[] = {h->dmodel, h->state, h->contacts, h->ccount, h->hitmask, h->stats, h->d_action, h->d_u, h->d_draws, h->d_obs, h->d_final, h->d_reward, h->d_term, h->d_trunc, h->d_succ, h->d_mask, h->d_nticks, h->d_defer};
   for (void* p : ptrs) if (p) cudaFree(p);
   if (h->own_stream) cudaStreamDestroy(h->own_stream);
+  if (h->order_evt) cudaEventDestroy(h->order_evt);
   delete h;
   return URGYM_OK;
 }
@@ -218,6 +232,7 @@ int urgym_step_host(urgym_handle h, const real* action, const real* u, const rea
   if (!h || !action || !obs || !reward || !terminated || !truncated || !success) return fail(URGYM_E_ARG, "urgym_step_host: null argument");
   CK(cudaSetDevice(h->device));
   size_t n = (size_t)h->N; int od = h->hmodel.obs_dim, ad = h->hmodel.act_dim; cudaStream_t st = h->own_stream;
+  { int rc = order_after_last(h, st); if (rc) return rc; }
   CK(cudaMemcpyAsync(h->d_action, action, n * ad * sizeof(real), cudaMemcpyHostToDevice, st));
   if (u) CK(cudaMemcpyAsync(h->d_u, u, n * sizeof(real), cudaMemcpyHostToDevice, st));
   if (draws) CK(cudaMemcpyAsync(h->d_draws, draws, n * 4 * sizeof(real), cudaMemcpyHostToDevice, st));
@@ -239,6 +254,7 @@ int urgym_reset_host(urgym_handle h, const uint8_t* mask, const real* draws, rea
   if (!h || !obs) return fail(URGYM_E_ARG, "urgym_reset_host: null argument");
   CK(cudaSetDevice(h->device));
   size_t n = (size_t)h->N; int od = h->hmodel.obs_dim; cudaStream_t st = h->own_stream;
+  { int rc = order_after_last(h, st); if (rc) return rc; }
   if (mask) CK(cudaMemcpyAsync(h->d_mask, mask, n, cudaMemcpyHostToDevice, st));
   if (draws) CK(cudaMemcpyAsync(h->d_draws, draws, n * 4 * sizeof(real), cudaMemcpyHostToDevice, st));
   if (mask) CK(cudaMemcpyAsync(h->d_obs, obs, n * od * sizeof(real), cudaMemcpyHostToDevice, st));  // unmasked rows keep the caller's values
@@ -254,31 +270,35 @@ int urgym_get_state(urgym_handle h, real* state_dev, void* stream) {
   if (!h || !state_dev) return fail(URGYM_E_ARG, "urgym_get_state: null argument");
   CK(cudaSetDevice(h->device));
   cudaStream_t st = (cudaStream_t)stream;  // NULL = the legacy default stream, as in the CUDA runtime
+  { int rc = order_after_last(h, st); if (rc) return rc; }
   CK(cudaMemcpyAsync(state_dev, h->state, (size_t)h->N * UG_STATE * sizeof(real), cudaMemcpyDeviceToDevice, st));
-  h->last_stream = st; return URGYM_OK;
+  return URGYM_OK;
 }
 int urgym_set_state(urgym_handle h, const real* state_dev, void* stream) {
   if (!h || !state_dev) return fail(URGYM_E_ARG, "urgym_set_state: null argument");
   CK(cudaSetDevice(h->device));
   cudaStream_t st = (cudaStream_t)stream;  // NULL = the legacy default stream, as in the CUDA runtime
+  { int rc = order_after_last(h, st); if (rc) return rc; }
   CK(cudaMemcpyAsync(h->state, state_dev, (size_t)h->N * UG_STATE * sizeof(real), cudaMemcpyDeviceToDevice, st));
-  h->last_stream = st; return URGYM_OK;
+  return URGYM_OK;
 }
 int urgym_contacts(urgym_handle h, int32_t* pairs_dev, int32_t* count_dev, void* stream) {
   if (!h || !pairs_dev || !count_dev) return fail(URGYM_E_ARG, "urgym_contacts: null argument");
   CK(cudaSetDevice(h->device));
   cudaStream_t st = (cudaStream_t)stream;  // NULL = the legacy default stream, as in the CUDA runtime
+  { int rc = order_after_last(h, st); if (rc) return rc; }
   CK(cudaMemcpyAsync(pairs_dev, h->contacts, (size_t)h->N * UG_MAXC * 2 * sizeof(int32_t), cudaMemcpyDeviceToDevice, st));
   CK(cudaMemcpyAsync(count_dev, h->ccount, (size_t)h->N * sizeof(int32_t), cudaMemcpyDeviceToDevice, st));
-  h->last_stream = st; return URGYM_OK;
+  return URGYM_OK;
 }
 
 int urgym_contact_pairs(urgym_handle h, uint32_t* mask_dev, void* stream) {
   if (!h || !mask_dev) return fail(URGYM_E_ARG, "urgym_contact_pairs: null argument");
   CK(cudaSetDevice(h->device));
   cudaStream_t st = (cudaStream_t)stream;
+  { int rc = order_after_last(h, st); if (rc) return rc; }
   CK(cudaMemcpyAsync(mask_dev, h->hitmask, (size_t)h->N * UG_HITWORDS * sizeof(uint32_t), cudaMemcpyDeviceToDevice, st));
-  h->last_stream = st; return URGYM_OK;
+  return URGYM_OK;
 }
 int urgym_num_pairs(int t) { DevModel m; return build_model(t, &m) ? URGYM_E_ARG : m.npairs; }
 int urgym_pair_info(int t, int pair, int* shape_a, int* shape_b) {

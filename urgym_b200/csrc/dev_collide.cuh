@@ -3,6 +3,7 @@
 // contact-breaking threshold, as pybullet's getContactPoints does. Stateless.
 #pragma once
 #include "dev_math.cuh"
+#include "model.h"
 
 struct BoxW { f3 c; m3 R; f3 h; };
 struct CPt { f3 posA, posB, n; real dist; };  // n from B to A
@@ -151,4 +152,166 @@ UG_DEV bool sphere_box(f3 sc, real r, const BoxW& B, real margin, f3& on_box, f3
   on_box = B.c + mulv(B.R, cl);
   n_bs = mulv(B.R, nl);
   return true;
+}
+
+// ---------------------------------------------------------------------------------------------------------------
+// Convex polytope (gripper link with mesh geometry; Bullet collides the convex hull of the mesh vertices) against a box
+// or a sphere: separating axes over the polytope's face normals, the box's face normals and the cross products of their
+// edge directions; then the incident face is clipped against the side planes of the reference face (polyhedral contact
+// clipping, the box-box scheme above with face lists). Same acceptance rule as box_box: points within `margin` of the
+// reference face, at most four, spread from the deepest. o / R: world frame of the link that carries the polytope.
+UG_DEV int clip_halfspace(f3* poly, int n, f3 o, f3 m) {
+  f3 out[24]; int k = 0;
+  for (int i = 0; i < n; i++) {
+    f3 P = poly[i], Q = poly[(i + 1 == n) ? 0 : i + 1];
+    real dp = dot(m, P - o), dq = dot(m, Q - o);
+    if (dp >= 0._r) out[k++] = P;
+    if ((dp >= 0._r) != (dq >= 0._r)) { real t = dp / (dp - dq); out[k++] = P + (Q - P) * t; }
+  }
+  if (k > 16) k = 16;
+  for (int i = 0; i < k; i++) poly[i] = out[i];
+  return k;
+}
+
+__device__ __noinline__ int poly_box(const DevPoly& P, f3 o, const m3& R, const BoxW& B, real margin, CPt* out) {
+  f3 v[UG_POLY_MAXV];
+  const int nv = P.nv, nf = P.nf, ne = P.ne;
+#pragma unroll 1
+  for (int i = 0; i < nv; i++) v[i] = o + mulv(R, ld3(P.v[i]));
+  const f3 bax[3] = {col(B.R, 0), col(B.R, 1), col(B.R, 2)};
+  real best = -1e30_r; int kind = 0, idx = 0, sgn = 1; f3 nBA = mk3(0, 0, 1);
+#pragma unroll 1
+  for (int f = 0; f < nf; f++) {                   // faces of the polytope: lowest point of the box above the face plane
+    const f3 n = mulv(R, ld3(P.fn[f]));
+    const real fd = P.fn[f][3] + dot(n, o);
+    const real sB = dot(n, B.c) - (B.h.x * rabs(dot(n, bax[0])) + B.h.y * rabs(dot(n, bax[1])) + B.h.z * rabs(dot(n, bax[2])));
+    const real s = sB - fd;
+    if (s > margin) return 0;
+    if (s > best) { best = s; kind = 0; idx = f; nBA = -n; }
+  }
+#pragma unroll 1
+  for (int j = 0; j < 3; j++) {                    // faces of the box: extent of the polytope along the box axis
+    real lo = 1e30_r, hi = -1e30_r;
+#pragma unroll 1
+    for (int i = 0; i < nv; i++) { real p = dot(bax[j], v[i] - B.c); lo = rmin(lo, p); hi = rmax(hi, p); }
+    const real hj = comp(B.h, j), sp = lo - hj, sm = -hi - hj;
+    if (sp > margin || sm > margin) return 0;
+    if (sp > best) { best = sp; kind = 1; idx = j; sgn = 1; nBA = bax[j]; }
+    if (sm > best) { best = sm; kind = 1; idx = j; sgn = -1; nBA = -bax[j]; }
+  }
+  int ea = 0, eb = 0;
+#pragma unroll 1
+  for (int e = 0; e < ne; e++) {
+    const f3 ed = mulv(R, ld3(P.ed[e]));
+#pragma unroll 1
+    for (int j = 0; j < 3; j++) {                  // edge x edge
+      f3 L = cross(ed, bax[j]); const real l = norm3(L);
+      if (l <= 1e-9_r) continue;
+      L = L * (1.0_r / l);
+      real mnA = 1e30_r, mxA = -1e30_r;
+#pragma unroll 1
+      for (int i = 0; i < nv; i++) { real p = dot(L, v[i] - B.c); mnA = rmin(mnA, p); mxA = rmax(mxA, p); }
+      const real rB = B.h.x * rabs(dot(L, bax[0])) + B.h.y * rabs(dot(L, bax[1])) + B.h.z * rabs(dot(L, bax[2]));
+      const real s1 = mnA - rB, s2 = -mxA - rB, sx = rmax(s1, s2);
+      if (sx > margin) return 0;
+      if (edge_bias(sx) > best) { best = sx; kind = 2; ea = e; eb = j; nBA = s1 >= s2 ? L : -L; }
+    }
+  }
+  if (kind == 2) {                                 // one point: closest points of the two supporting edges
+    real exA = 1e30_r;
+    for (int i = 0; i < nv; i++) exA = rmin(exA, dot(nBA, v[i]));
+    f3 pa = mk3(0, 0, 0); int ca = 0;
+    for (int i = 0; i < nv; i++) if (dot(nBA, v[i]) <= exA + 1e-5_r) { pa = pa + v[i]; ca++; }
+    pa = pa * (1.0_r / (real)ca);
+    f3 pb = B.c;
+#pragma unroll
+    for (int k = 0; k < 3; k++) if (k != eb) pb = pb + bax[k] * ((dot(nBA, bax[k]) > 0._r ? 1.0_r : -1.0_r) * comp(B.h, k));
+    const f3 ua = mulv(R, ld3(P.ed[ea])), ub = bax[eb], d = pb - pa;
+    const real uaub = dot(ua, ub), q1 = dot(ua, d), q2 = -dot(ub, d), den = 1.0_r - uaub * uaub;
+    real beta = 0._r;
+    if (den > 1e-4_r) beta = (uaub * q1 + q2) / den;
+    pb = pb + ub * beta;
+    out[0].n = nBA; out[0].dist = best; out[0].posB = pb; out[0].posA = pb + nBA * best;
+    return 1;
+  }
+  f3 poly[24]; int n = 0; f3 rn; real rd;
+  if (kind == 0) {                                 // reference face on the polytope; incident = the box face most against it
+    rn = mulv(R, ld3(P.fn[idx])); rd = P.fn[idx][3] + dot(rn, o);
+    int la = 0; real lav = -1._r;
+#pragma unroll
+    for (int j = 0; j < 3; j++) { real t = rabs(dot(rn, bax[j])); if (t > lav) { lav = t; la = j; } }
+    const int a1 = (la + 1) % 3, a2 = (la + 2) % 3;
+    const real sg = dot(rn, bax[la]) > 0._r ? -1.0_r : 1.0_r;
+    const f3 fc = B.c + bax[la] * (sg * comp(B.h, la)), e1 = bax[a1] * comp(B.h, a1), e2 = bax[a2] * comp(B.h, a2);
+    poly[0] = fc - e1 - e2; poly[1] = fc + e1 - e2; poly[2] = fc + e1 + e2; poly[3] = fc - e1 + e2; n = 4;
+    const int cnt = P.fcount[idx];
+    for (int k = 0; k < cnt && n > 0; k++) {
+      const f3 a = v[P.floop[idx][k]], e = v[P.floop[idx][(k + 1 == cnt) ? 0 : k + 1]] - a;
+      n = clip_halfspace(poly, n, a, cross(rn, e));
+    }
+  } else {                                         // reference face on the box; incident = the polytope's face most against it
+    rn = bax[idx] * (real)sgn; rd = dot(rn, B.c) + comp(B.h, idx);
+    int fi = 0; real fv = 1e30_r;
+#pragma unroll 1
+    for (int f = 0; f < nf; f++) { real t = dot(mulv(R, ld3(P.fn[f])), rn); if (t < fv) { fv = t; fi = f; } }
+    const int cnt = P.fcount[fi];
+    for (int k = 0; k < cnt; k++) poly[n++] = v[P.floop[fi][k]];
+    const int c1 = (idx + 1) % 3, c2 = (idx + 2) % 3;
+    for (int t = 0; t < 4 && n > 0; t++) {
+      const int c = t < 2 ? c1 : c2;
+      const f3 ax = bax[c] * ((t & 1) ? -1.0_r : 1.0_r);
+      n = clip_halfspace(poly, n, B.c + ax * comp(B.h, c), -ax);
+    }
+  }
+  real dist[16]; int m = 0;
+  for (int i = 0; i < n; i++) {
+    const real dv = dot(rn, poly[i]) - rd;
+    if (dv <= margin) { poly[m] = poly[i]; dist[m] = dv; m++; }
+  }
+  if (m == 0) return 0;
+  int cnt = m < 4 ? m : 4, i0 = 0;
+  if (m > 4) for (int t = 1; t < m; t++) if (-dist[t] > -dist[i0]) i0 = t;
+  for (int j = 0; j < cnt; j++) {
+    const int sl = m > 4 ? (i0 + (j * m) / 4) % m : j;
+    const f3 pt = poly[sl]; const real dv = dist[sl];
+    out[j].n = nBA; out[j].dist = dv;
+    if (kind == 0) { out[j].posB = pt; out[j].posA = pt + nBA * dv; }
+    else { out[j].posA = pt; out[j].posB = pt - nBA * dv; }
+  }
+  return cnt;
+}
+
+// Closest point of the polytope to a sphere centre, like sphere_box: point on the polytope, normal towards the sphere.
+__device__ __noinline__ bool sphere_poly(f3 sc, real r, const DevPoly& P, f3 o, const m3& R, real margin, f3& on_poly, f3& n_ps, real& dist) {
+  const int nf = P.nf;
+  real mx = -1e30_r; int fm = 0;
+#pragma unroll 1
+  for (int f = 0; f < nf; f++) { const f3 n = mulv(R, ld3(P.fn[f])); real s = dot(n, sc) - (P.fn[f][3] + dot(n, o)); if (s > mx) { mx = s; fm = f; } }
+  if (mx <= 0._r) {
+    const f3 n = mulv(R, ld3(P.fn[fm]));
+    n_ps = n; on_poly = sc - n * mx; dist = mx - r;
+  } else {
+    real bd = 1e30_r; f3 bp = sc;
+#pragma unroll 1
+    for (int f = 0; f < nf; f++) {
+      const f3 n = mulv(R, ld3(P.fn[f]));
+      const real s = dot(n, sc) - (P.fn[f][3] + dot(n, o));
+      if (s <= 0._r) continue;
+      const f3 q = sc - n * s;
+      const int cnt = P.fcount[f];
+      bool inside = true; real be = 1e30_r; f3 bq = q;
+      for (int k = 0; k < cnt; k++) {
+        const f3 a = o + mulv(R, ld3(P.v[P.floop[f][k]])), e = o + mulv(R, ld3(P.v[P.floop[f][(k + 1 == cnt) ? 0 : k + 1]])) - a;
+        if (dot(cross(n, e), q - a) < 0._r) inside = false;
+        real t = dot(sc - a, e) / dot(e, e); t = rmin(1.0_r, rmax(0._r, t));
+        const f3 c = a + e * t; const real d2 = dot(sc - c, sc - c);
+        if (d2 < be) { be = d2; bq = c; }
+      }
+      const f3 cp = inside ? q : bq; const real d2 = inside ? s * s : be;
+      if (d2 < bd) { bd = d2; bp = cp; }
+    }
+    const real len = rsqrt_(bd);
+    on_poly = bp; n_ps = (sc - bp) * (1.0_r / len); dist = len - r;
+  }
+  return dist < margin;
 }

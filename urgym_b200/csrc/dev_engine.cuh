@@ -27,7 +27,7 @@ struct Con {
 template <int NCAP, int RC>
 struct SmemT {
   static constexpr int NC_CAP = NCAP;  // manifold points kept per tick
-  static constexpr int TSQ = RC * RC + 32;  // + slack: lanes without a row still issue the (unused) operand load
+  static constexpr int TTRI = RC * (RC + 1) / 2;  // packed lower triangle of the symmetric contact block
   // ---- state that lives across the ticks of one gym step
   real q[UG_NDOF], qd[UG_NDOF], tgt[8];
   real fpos[UG_MAXFREE][3], fquat[UG_MAXFREE][4], flin[UG_MAXFREE][3], fang[UG_MAXFREE][3];
@@ -45,7 +45,10 @@ struct SmemT {
   // rows 0..16: extended M^-1 (17 x 17); rows 17..: robot velocity response of each contact row in the same 17 columns
   real E[(UG_NCOL + RC) * UG_NCOL];
   union alignas(16) {
-    real T[TSQ];  // contact-space Delassus block, full symmetric RC x RC: a step of row r reads row r, lane = own row
+    // Contact-space Delassus block T = J M^-1 J^T, symmetric, packed lower triangle: T(r, c) at r (r + 1) / 2 + c for c <= r.
+    // A step of row r reads T(r, c) for the lane's own rows c: c <= r is contiguous in c, c > r sits at c (c + 1) / 2 + r, and
+    // consecutive triangular numbers are distinct modulo 32 (16 o + l (l + 1) / 2 for c = 32 o + l), so both are conflict-free.
+    real T[TTRI];
     struct {
       real M[UG_NDOF][UG_NDOF];  // mass matrix, then M^-1 (16-byte aligned rows for the row build)
       real cm[UG_NDOF][3], Iw[UG_NDOF][6];

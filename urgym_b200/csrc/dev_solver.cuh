@@ -88,7 +88,8 @@ __device__ __noinline__ void collide(S& s, const DevModel& M, const Gp<G> gp) {
       const real margin = rmin(A.cbt, B.cbt);
       BoxW a, b; shape_box(s, A, a); shape_box(s, B, b);
       const f3 dc = a.c - b.c;
-      if (A.kind == 0 && B.kind == 0) n = box_box(a, b, margin, pts);
+      if (A.kind != 1 && B.kind == 0) n = box_box(a, b, margin, pts);   // a polytope's bounding box: the mid-phase
+      else if (A.kind == 2) { f3 oa, na; real d; n = sphere_box(b.c, B.radius, a, margin, oa, na, d) ? 1 : 0; }
       else if (A.kind == 1 && B.kind == 0) {
         f3 ob, nb; real d;
         if (sphere_box(a.c, A.radius, b, margin, ob, nb, d)) { pts[0].n = nb; pts[0].dist = d; pts[0].posB = ob; pts[0].posA = ob + nb * d; n = 1; }
@@ -101,6 +102,21 @@ __device__ __noinline__ void collide(S& s, const DevModel& M, const Gp<G> gp) {
           f3 nn = len > 1e-12_r ? dc * (1.0_r / len) : mk3(1, 0, 0);
           pts[0].n = nn; pts[0].dist = d; pts[0].posB = b.c + nn * B.radius; pts[0].posA = pts[0].posB + nn * d; n = 1;
         }
+      }
+    }
+    // robot links with mesh geometry whose bounding box is close: the polytope itself decides (few lanes, rarely)
+    if (n > 0 && M.shapes[sa].kind == 2) {
+      const DevShape& A = M.shapes[sa]; const DevShape& B = M.shapes[sb];
+      const real margin = rmin(A.cbt, B.cbt);
+      const int lb = M.link_body[A.link];
+      const m3 Rb = ldm(s.bR[lb]);
+      const f3 o = ld3(s.bp[lb]) + mulv(Rb, ld3(M.link_lpos[A.link]));
+      const m3 Rl = mulm(Rb, ldm(M.link_lrot[A.link]));
+      BoxW b; shape_box(s, B, b);
+      if (B.kind == 0) n = poly_box(M.polys[A.poly], o, Rl, b, margin, pts);
+      else {
+        f3 oa, na; real d; n = 0;
+        if (sphere_poly(b.c, B.radius, M.polys[A.poly], o, Rl, margin, oa, na, d)) { pts[0].n = -na; pts[0].dist = d; pts[0].posA = oa; pts[0].posB = oa + na * d; n = 1; }
       }
     }
     int incl = n;
@@ -374,7 +390,7 @@ __device__ __noinline__ real solve_and_integrate(S& s, const DevModel& M, const 
       }
     }
     const int cmax = min(Rc, so * G + G);
-    real* Trow = s.u.T + c * RC;
+    real* Trow = s.u.T + (c * (c + 1)) / 2;   // packed lower triangle: this lane writes T(c, cp) for cp <= c
 #pragma unroll 1
     for (int cp = 0; cp < cmax; cp++) {
       const int dp = s.cdesc[cp], tp = (dp >> 8) & 15;
@@ -398,7 +414,7 @@ __device__ __noinline__ real solve_and_integrate(S& s, const DevModel& M, const 
           acc -= dot(dv, vel);
         }
       }
-      if (has) { Trow[cp] = acc; if (cp < so * G) s.u.T[cp * RC + c] = acc; }  // rows of earlier slots get their upper part here
+      if (has && cp <= c) Trow[cp] = acc;   // T(c, cp) with cp > c is the owner of row cp's entry
     }
   }
   gp.sync();
@@ -410,7 +426,11 @@ __device__ __noinline__ real solve_and_integrate(S& s, const DevModel& M, const 
 #pragma unroll
   for (int k = 0; k < NSJ; k++) { aEj[k] = aE + UG_RB * (unsigned)(colown[k] * UG_NCOL); aEq[k] = aE + UG_RB * (unsigned)(UG_NCOL * UG_NCOL + colown[k]); }
   const unsigned aEc = aE + UG_RB * (unsigned)((UG_NCOL + l) * UG_NCOL);  // contact slot o: + o * G * UG_NCOL * 4
-  const unsigned aTl = aT + UG_RB * (unsigned)l;                           // row r: + r * RC * 4; contact slot o: + o * G * 4
+  // T(r, c) for the lane's row c = l + G o of contact slot o: c <= r -> aTrow[o] + tri(r), c > r -> aTcol[o] + r (in scalars).
+  // Lanes beyond the last row address the last row (their operand is never used).
+  unsigned aTrow[NSC], aTcol[NSC];
+#pragma unroll
+  for (int o = 0; o < NSC; o++) { const int c_ = min(l + G * o, RC - 1); aTrow[o] = aT + UG_RB * (unsigned)c_; aTcol[o] = aT + UG_RB * (unsigned)((c_ * (c_ + 1)) / 2); }
   real limv[NSC];
 #pragma unroll
   for (int so = 0; so < NSC; so++) limv[so] = 0._r;
@@ -438,11 +458,15 @@ __device__ __noinline__ real solve_and_integrate(S& s, const DevModel& M, const 
   }
   // operands of a contact-row step (rows ROW and, when PAIR, ROW + 1): E entries for the joint slots, T entries for
   // the contact slots
-#define UG_CONTACT_LOAD(ROW, PAIR, NACT)                                                                 \
-    const unsigned er_ = UG_RB * (unsigned)((ROW) * UG_NCOL), tr_ = aTl + UG_RB * (unsigned)((ROW) * RC);      \
+  // SO = the (compile-time) contact slot of the stepping row: slots below it hold only rows c < ROW, slots above only c > ROW
+#define UG_T_ADDR(o_, SO, ROW, TRI) ((o_) < (SO) ? aTrow[o_] + (TRI) : ((o_) > (SO) ? aTcol[o_] + UG_RB * (unsigned)(ROW) : \
+                                     ((l + G * (o_)) <= (ROW) ? aTrow[o_] + (TRI) : aTcol[o_] + UG_RB * (unsigned)(ROW))))
+#define UG_CONTACT_LOAD(ROW, SO, PAIR, NACT)                                                             \
+    const unsigned er_ = UG_RB * (unsigned)((ROW) * UG_NCOL);                                           \
+    const unsigned t0_ = UG_RB * (unsigned)(((ROW) * ((ROW) + 1)) >> 1), t1_ = t0_ + UG_RB * (unsigned)((ROW) + 1); \
     real uj_[NSJ], vj_[NSJ], uc_[NACT], vc_[NACT];                                                      \
     _Pragma("unroll") for (int k_ = 0; k_ < NSJ; k_++) { uj_[k_] = lds(aEq[k_] + er_); vj_[k_] = (PAIR) ? lds(aEq[k_] + er_ + UG_RB * UG_NCOL) : 0._r; } \
-    _Pragma("unroll") for (int o_ = 0; o_ < (NACT); o_++) { uc_[o_] = lds(tr_ + UG_RB * (unsigned)(o_ * G)); vc_[o_] = (PAIR) ? lds(tr_ + UG_RB * (unsigned)(RC + o_ * G)) : 0._r; }
+    _Pragma("unroll") for (int o_ = 0; o_ < (NACT); o_++) { uc_[o_] = lds(UG_T_ADDR(o_, SO, ROW, t0_)); vc_[o_] = (PAIR) ? lds(UG_T_ADDR(o_, SO, (ROW) + 1, t1_)) : 0._r; }
 #define UG_CONTACT_APPLY(DA, DB, PAIR, NACT)                                                             \
     _Pragma("unroll") for (int k_ = 0; k_ < NSJ; k_++) { w[k_] = rfma(uj_[k_], DA, w[k_]); if (PAIR) w[k_] = rfma(vj_[k_], DB, w[k_]); } \
     _Pragma("unroll") for (int o_ = 0; o_ < (NACT); o_++) { w[NSJ + o_] = rfma(uc_[o_], DA, w[NSJ + o_]); if (PAIR) w[NSJ + o_] = rfma(vc_[o_], DB, w[NSJ + o_]); }
@@ -474,7 +498,7 @@ __device__ __noinline__ real solve_and_integrate(S& s, const DevModel& M, const 
   {                                                                                                      \
     const real nlo = lo[NSJ] - lam[NSJ], nhi = hi[NSJ] - lam[NSJ];   /* constant over the sweep, as above */ \
     _Pragma("unroll 1") for (int row = 0; row < NC; row++) {                                             \
-      UG_CONTACT_LOAD(row, false, NACT)                                                                  \
+      UG_CONTACT_LOAD(row, 0, false, NACT)                                                               \
       real d_ = rfma(-w[NSJ], invd[NSJ], rhs[NSJ]);                                                     \
       d_ = rmin(rmax(d_, nlo), nhi);                                                                   \
       const real delta = gp.shfl(d_, row);                                                              \
@@ -486,7 +510,7 @@ __device__ __noinline__ real solve_and_integrate(S& s, const DevModel& M, const 
       _Pragma("unroll") for (int so = 0; so < (NACT); so++) {                                            \
         const int a_ = max(NC, so * G), b_ = min(NC + NT, so * G + G);                                   \
         _Pragma("unroll 1") for (int row = a_; row < b_; row++) {                                        \
-          UG_CONTACT_LOAD(row, false, NACT)                                                              \
+          UG_CONTACT_LOAD(row, so, false, NACT)                                                          \
           const real bnd = limv[so];                                                                    \
           real d_ = rfma(-w[NSJ + so], invd[NSJ + so], rhs[NSJ + so]);                                  \
           d_ = rmin(rmax(d_, -bnd - lam[NSJ + so]), bnd - lam[NSJ + so]);                              \
@@ -500,7 +524,7 @@ __device__ __noinline__ real solve_and_integrate(S& s, const DevModel& M, const 
     _Pragma("unroll") for (int so = 0; so < (NACT); so++) {                                              \
       const int a_ = max(fr0, so * G), b_ = min(Rc, so * G + G);                                         \
       _Pragma("unroll 1") for (int row = a_; row < b_; row += 2) {                                       \
-        UG_CONTACT_LOAD(row, true, NACT)                                                                 \
+        UG_CONTACT_LOAD(row, so, true, NACT)                                                             \
         const int li = row - so * G;                                                                     \
         real d_ = rfma(-w[NSJ + so], invd[NSJ + so], rhs[NSJ + so]);                                    \
         const real sm = lam[NSJ + so] + d_;                                                             \
@@ -551,6 +575,7 @@ __device__ __noinline__ real solve_and_integrate(S& s, const DevModel& M, const 
   }
 #undef UG_JOINT_STEP
 #undef UG_CONTACT_LOAD
+#undef UG_T_ADDR
 #undef UG_CONTACT_APPLY
 #undef UG_JOINT_SWEEP
 #undef UG_CONTACT_SWEEP

@@ -19,8 +19,22 @@
 #define UG_STATE 96
 #define UG_ENV_COUNT 7  // 0 BallBalance 1 TwoBallsBalance 2 CubesPush 3 CubesGrasp 4 Golf 5 CubesPushDiff 6 GolfJoints
 
+// Convex polytope of a gripper link whose collision geometry is a mesh (model_data.h: URG_POLYS), in the link frame.
+#define UG_NPOLY 5
+#define UG_POLY_MAXV 16
+#define UG_POLY_MAXF 32
+#define UG_POLY_MAXL 8
+#define UG_POLY_MAXE 12
+struct DevPoly {
+  int nv, nf, ne, pad;
+  real v[UG_POLY_MAXV][3]; real fn[UG_POLY_MAXF][4];   // vertices; face planes n . x = d (outward)
+  uint8_t fcount[UG_POLY_MAXF]; uint8_t floop[UG_POLY_MAXF][UG_POLY_MAXL];  // CCW vertex loop per face
+  real ed[UG_POLY_MAXE][3];                             // edge directions used for the edge-edge separating axes
+};
+
 struct DevShape {
-  int kind;    // 0 box, 1 sphere
+  int kind;    // 0 box, 1 sphere, 2 convex polytope (robot link; lc / lR / half then hold its bounding box for the mid-phase)
+  int poly;    // kind 2: index into DevModel::polys; the polytope lives in the frame of Bullet link `link`
   int body;    // 0 robot, 1..3 free body, -1 static
   int link;    // Bullet link index (robot) or sub-shape id
   int rbody;   // robot shapes: index of the movable body (dof) that carries the link
@@ -47,6 +61,7 @@ struct DevModel {
   // broad-phase bound per pair: the pair can only produce manifold points (separating-axis slack <= margin on all 15 axes)
   // while the centre distance (static partner: distance from the centre to the static box) is <= cullr (model_build.cpp)
   real cullr[UG_MAXPAIRS];
+  DevPoly polys[UG_NPOLY];
 };
 
 // Host: fills *m for env_type 0..UG_ENV_COUNT-1. Returns 0 or -1.

@@ -148,6 +148,7 @@ int build_model(int env_type_full, DevModel* m) {
     DevShape s = mk_box(0, li, lc, L.box_half, 0.5);
     for (int i = 0; i < 9; i++) s.lR[i] = (real)R.m[i];
     s.rbody = carrier[li];
+    if (URG_LINK_POLY[li] >= 0) { s.kind = 2; s.poly = URG_LINK_POLY[li]; }  // mesh geometry: convex polytope, the box is its bound
     m->shapes[ns++] = s;
   }
   const double table_c[3] = {0, 0, -0.25}, table_h[3] = {0.5, 1.0, 0.25}, zero[3] = {0, 0, 0};
@@ -213,6 +214,19 @@ int build_model(int env_type_full, DevModel* m) {
   }
   if (env_type_full == 6) { m->obs_dim = 15; m->act_dim = 6; }   // env_golf_joints_v0.py:60-63
   m->nshapes = ns;
+  static_assert(URG_NPOLY == UG_NPOLY && URG_POLY_MAXV == UG_POLY_MAXV && URG_POLY_MAXF == UG_POLY_MAXF && URG_POLY_MAXL == UG_POLY_MAXL &&
+                URG_POLY_MAXE == UG_POLY_MAXE, "model_data.h and model.h disagree on the polytope capacities");
+  for (int k = 0; k < UG_NPOLY; k++) {
+    const UrgPoly& P = URG_POLYS[k]; DevPoly& D = m->polys[k];
+    D.nv = P.nv; D.nf = P.nf; D.ne = P.ne;
+    for (int i = 0; i < P.nv; i++) for (int c = 0; c < 3; c++) D.v[i][c] = (real)P.v[i][c];
+    for (int f = 0; f < P.nf; f++) {
+      for (int c = 0; c < 4; c++) D.fn[f][c] = (real)P.fn[f][c];
+      D.fcount[f] = (uint8_t)P.fcount[f];
+      for (int c = 0; c < P.fcount[f]; c++) D.floop[f][c] = (uint8_t)P.floop[f][c];
+    }
+    for (int e = 0; e < P.ne; e++) for (int c = 0; c < 3; c++) D.ed[e][c] = (real)P.ed[e][c];
+  }
   int np = 0;
   auto add = [&](int a, int b) { if (np < UG_MAXPAIRS) { m->pairs[np][0] = (uint8_t)a; m->pairs[np][1] = (uint8_t)b; } np++; };
   for (int a = 0; a < ns; a++) for (int b = a + 1; b < ns; b++) if (m->shapes[a].body > 0 && m->shapes[b].body > 0 && m->shapes[a].body != m->shapes[b].body) add(a, b);

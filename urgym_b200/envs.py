@@ -17,6 +17,7 @@ Two entry points:
 Everything physical happens in liburgym_b200.so through the C ABI (include/urgym_b200.h). There is no CPU fallback.
 """
 import math
+import os
 
 import numpy as np
 
@@ -74,14 +75,14 @@ def _spaces(env_id):
 class URGymVectorEnv:
     """`num_envs` independent instances of one env on one GPU; tensors stay on the device."""
 
-    def __init__(self, env_id, num_envs, device=0, seed=0, reward_type='dense', env_index_offset=0, render_mode=None, camera=None):
+    def __init__(self, env_id, num_envs, device=0, seed=None, reward_type='dense', env_index_offset=0, render_mode=None, camera=None):
         from .batch import EnvBatch  # imports torch; needs CUDA
         if env_id not in SPECS:
             raise ValueError('%s is not backed by urgym_b200 (supported: %s)' % (env_id, ', '.join(SPECS)))
         self.env_id, self.name, self.max_episode_steps = env_id, SPECS[env_id][0], SPECS[env_id][1]
         self.num_envs = int(num_envs)
         self.single_observation_space, self.single_action_space = _spaces(env_id)
-        self.batch = EnvBatch(self.name, self.num_envs, device=device, seed=seed, env_index_offset=env_index_offset,
+        self.batch = EnvBatch(self.name, self.num_envs, device=device, seed=_fresh_seed() if seed is None else seed, env_index_offset=env_index_offset,
                               reward_sparse=(reward_type == 'sparse'))
         self.device = self.batch.device
 
@@ -109,12 +110,21 @@ class URGymVectorEnv:
         self.batch.close()
 
 
-class _SingleEnv:
+def _fresh_seed():
+    """The reference draws its spawn positions from the unseeded global `random` (env_ball_balance_v0.py:193-194): two envs
+    built without a seed must not replay the same episodes."""
+    return int.from_bytes(os.urandom(7), 'little')
+
+
+_EnvBase = _gym.Env if _gym is not None else object   # gym.make() needs a gymnasium.Env (spec, unwrapped, the passive checker)
+
+
+class _SingleEnv(_EnvBase):
     """Batch-of-one env with the reference's single-env signature (numpy in / out, float64 observations)."""
     env_id = None
     metadata = {'render_modes': ['human', 'train']}
 
-    def __init__(self, camera=None, reward_type='dense', render_mode='human', device=0, seed=0):
+    def __init__(self, camera=None, reward_type='dense', render_mode='human', device=0, seed=None):
         # render_mode='human' opens a pybullet GUI in the reference (env_ball_balance_v0.py:45-57); there is no GUI
         # here, the argument is accepted and ignored. `camera` is always None in the reference.
         import torch
@@ -123,9 +133,13 @@ class _SingleEnv:
         self.name, self.max_episode_steps = SPECS[self.env_id][0], SPECS[self.env_id][1]
         self.observation_space, self.action_space = _spaces(self.env_id)
         self.reward_type = reward_type
-        self.batch = EnvBatch(self.name, 1, device=device, seed=seed, reward_sparse=(reward_type == 'sparse'))
+        self.render_mode = render_mode
+        self.batch = EnvBatch(self.name, 1, device=device, seed=_fresh_seed() if seed is None else seed, reward_sparse=(reward_type == 'sparse'))
 
     def reset(self, *, seed=None, options=None):
+        # as in the reference, `seed` reaches only Env.np_random (super().reset), which the envs never draw from
+        if _gym is not None:
+            super().reset(seed=seed)
         draws = (options or {}).get('draws')
         obs = self.batch.reset(draws=None if draws is None else np.asarray(draws, dtype=np.float32).reshape(1, 4))
         return obs[0].double().cpu().numpy(), {}
@@ -165,7 +179,9 @@ def make(env_id, **kwargs):
 
 
 def register_all():
-    """Register the five ids with gymnasium when it is installed (same ids and limits as urgym/envs/__init__.py)."""
+    """Register the ids with gymnasium when it is installed (same ids as urgym/envs/__init__.py; the TimeLimit is applied by the
+    backend, so no max_episode_steps is passed). gymnasium is not installed in this image or on the GPU box: this path is
+    untested here (INTEGRATION.md says so)."""
     if _gym is None:
         return False
     from gymnasium.envs.registration import register, registry
