@@ -75,6 +75,25 @@ int urgym_step(urgym_handle h, const urgym_real* action_dev, const urgym_real* u
                urgym_real* reward_dev, uint8_t* terminated_dev, uint8_t* truncated_dev, uint8_t* success_dev,
                urgym_real* final_obs_dev, int32_t* nticks_dev, int autoreset, void* stream);
 
+/* Allocation-free step. No counterpart in the reference: added for callers that
+ * cannot call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid it). One gym step of
+ * `num_envs` envs as urgym_step does it, but without a handle: the caller passes the state records in and out
+ * (state_in_dev / state_out_dev float[N,URGYM_STATE_FLOATS], as urgym_get_state returns them; the two may be the same
+ * buffer) together with what urgym_create would have fixed (env type, seed, env_index_offset, reward_sparse), and the
+ * working memory urgym_create would have allocated (scene model, finished-env flags, episode counters) lives in a static
+ * device array inside the library. The call itself performs no cudaMalloc / cudaFree and calls no allocating library
+ * routine. Limit: num_envs <= URGYM_STATIC_MAX_ENVS (16384); larger batches are rejected with URGYM_E_ARG. The first call
+ * per device writes the scene models into the array with blocking copies (make it outside a capture). Every call on a device
+ * shares the array: calls that overlap on the GPU (different streams) race on it; calls on one stream are safe.
+ * stats_dev double[8] (nullable): the counters of urgym_stats for THIS call only (they are cleared at the start of each call).
+ * Other arguments as in urgym_step. Results are bit-identical to urgym_step from the same state. */
+enum { URGYM_STATIC_MAX_ENVS = 16384 };
+int urgym_step_static(int env_type, int device, int num_envs, uint64_t seed, int env_index_offset, int reward_sparse,
+                      const urgym_real* state_in_dev, const urgym_real* action_dev, const urgym_real* u_dev, const urgym_real* draws_dev,
+                      urgym_real* state_out_dev, urgym_real* obs_dev, urgym_real* reward_dev, uint8_t* terminated_dev,
+                      uint8_t* truncated_dev, uint8_t* success_dev, urgym_real* final_obs_dev, int32_t* nticks_dev,
+                      double* stats_dev, int autoreset, void* stream);
+
 /* Same call with HOST buffers: copies inputs host->device and results device->host on the handle's stream and
  * synchronises. This is the entry the single-env Gymnasium shim and bench.py's e2e leg use. */
 int urgym_step_host(urgym_handle h, const urgym_real* action, const urgym_real* u, const urgym_real* draws, urgym_real* obs, urgym_real* reward,

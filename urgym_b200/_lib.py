@@ -16,6 +16,7 @@ STATE_FLOATS = 96
 MAX_CONTACTS = 32      # width of the manifold-point export (include/urgym_b200.h: URGYM_MAX_CONTACTS)
 PAIR_WORDS = 5         # uint32 words of the per-pair contact mask (URGYM_PAIR_WORDS)
 NUM_LINKS = 19
+STATIC_MAX_ENVS = 16384   # URGYM_STATIC_MAX_ENVS: largest batch of the allocation-free entry (urgym_step_static)
 
 _libs = {}
 
@@ -38,6 +39,7 @@ def lib(precision='f32'):
     L.urgym_destroy.argtypes = [vp]
     L.urgym_reset.argtypes = [vp, vp, vp, vp, vp, vp]
     L.urgym_step.argtypes = [vp] + [vp] * 10 + [i32, vp]
+    L.urgym_step_static.argtypes = [i32, i32, i32, u64, i32, i32] + [vp] * 13 + [i32, vp]
     L.urgym_step_host.argtypes = [vp] + [vp] * 10 + [i32]
     L.urgym_reset_host.argtypes = [vp, vp, vp, vp, vp]
     L.urgym_get_state.argtypes = [vp, vp, vp]

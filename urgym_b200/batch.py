@@ -157,3 +157,22 @@ def gripper_center(q, device=0, precision='f32'):
     L = _lib.lib(precision)
     check(L.urgym_gripper_center(device, q.shape[0], _ptr(q), _ptr(out), _stream(dev)), L)
     return out
+
+
+def step_static(env, state_in, action, out, u=None, draws=None, seed=0, env_index_offset=0, reward_sparse=False, autoreset=True,
+                precision='f32'):
+    """One gym step through the allocation-free entry (include/urgym_b200.h: urgym_step_static). Every buffer is the caller's:
+    `state_in` [n,96] and the dict `out` of preallocated device tensors {'state','obs','reward','terminated','truncated',
+    'success'} plus optional 'final_obs', 'nticks' [n,2] int32 and 'stats' [8] float64. No tensor is created here when the
+    inputs already are contiguous device tensors of the library's dtype."""
+    L = _lib.lib(precision)
+    env_type = ENV_TYPES[env] if isinstance(env, str) else int(env)
+    dev = state_in.device
+    n = state_in.shape[0]
+    dt = _DTYPE[precision]
+    a = _real(action, dev, (n, -1), dt)
+    check(L.urgym_step_static(env_type, dev.index or 0, n, seed, env_index_offset, int(reward_sparse), _ptr(state_in), _ptr(a),
+                              _ptr(_real(u, dev, (n,), dt)), _ptr(_real(draws, dev, (n, 4), dt)), _ptr(out['state']), _ptr(out['obs']),
+                              _ptr(out['reward']), _ptr(out['terminated']), _ptr(out['truncated']), _ptr(out['success']),
+                              _ptr(out.get('final_obs')), _ptr(out.get('nticks')), _ptr(out.get('stats')), int(autoreset), _stream(dev)), L)
+    return out

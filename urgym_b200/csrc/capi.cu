@@ -16,6 +16,21 @@
 #endif
 #include "kernels.cuh"
 
+// ---- urgym_step_static: the allocation-free entry (include/urgym_b200.h). Everything the launch needs besides the
+// caller's buffers lives in ONE file-scope device array, which every GPU that loads this library holds until exit: the
+// seven scene models (written once per device at set-up), the episode counters of the call (cleared by every call) and the
+// finished-env flags that carry the auto-reset of the ball scenes from the step grid to the reset-only grid (every flag
+// below num_envs is rewritten by the step grid before the reset grid reads it, so nothing there has to start at zero).
+// In host code the array's name is only a stand-in for the symbol: its device address comes from cudaGetSymbolAddress
+// with the device current, once per device.
+#define UG_STATIC_MAX_ENVS 16384
+struct StaticScratch {
+  DevModel model[UG_ENV_COUNT];
+  double stats[8];
+  uint8_t defer[UG_STATIC_MAX_ENVS];
+};
+static __device__ __align__(256) unsigned char g_static_scratch[(sizeof(StaticScratch) + 255) / 256 * 256];
+
 namespace {
 
 thread_local std::string g_err;
@@ -106,6 +121,51 @@ int launch(urgym_handle h, KParams& P, void* stream) {
     case 4: return launch_env<4>(h, P, st);
     case 5: return launch_env<5>(h, P, st);
     default: return launch_env<6>(h, P, st);
+  }
+}
+
+StaticScratch* g_static_ptr[16] = {nullptr};   // per device: the array's address on that device
+
+int static_setup(int device, StaticScratch** out) {
+  if (device < 0 || device >= 16) return fail(URGYM_E_ARG, "urgym_step_static: device out of range");
+  CK(cudaSetDevice(device));
+  if (!g_static_ptr[device]) {
+    StaticScratch* p = nullptr;
+    CK(cudaGetSymbolAddress((void**)&p, g_static_scratch));
+    for (int t = 0; t < UG_ENV_COUNT; t++) {
+      DevModel hm; if (build_model(t, &hm)) return fail(URGYM_E_ARG, "model build failed");
+      { const char* e = getenv("URGYM_GENERIC_SWEEPS"); hm.generic_sweeps = e && atoi(e) != 0; }
+      CK(cudaMemcpy(&p->model[t], &hm, sizeof(DevModel), cudaMemcpyHostToDevice));
+    }
+    g_static_ptr[device] = p;
+  }
+  *out = g_static_ptr[device];
+  return URGYM_OK;
+}
+
+template <int ENV>
+int launch_static(int N, int device, const KParams& P, cudaStream_t st) {
+  static bool attr_done[16] = {false};
+  const size_t smem = sizeof(EnvSmem<ENV>);
+  if (!attr_done[device]) {
+    CK(cudaFuncSetAttribute(env_kernel<ENV, 32>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    CK(cudaFuncSetAttribute(env_kernel<ENV, 32>, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared));
+    attr_done[device] = true;
+  }
+  env_kernel<ENV, 32><<<N, 32, smem, st>>>(P);
+  g_launches++;
+  CK(cudaGetLastError());
+  return URGYM_OK;
+}
+int launch_static_any(int env_type, int N, int device, const KParams& P, cudaStream_t st) {
+  switch (env_type) {
+    case 0: return launch_static<0>(N, device, P, st);
+    case 1: return launch_static<1>(N, device, P, st);
+    case 2: return launch_static<2>(N, device, P, st);
+    case 3: return launch_static<3>(N, device, P, st);
+    case 4: return launch_static<4>(N, device, P, st);
+    case 5: return launch_static<5>(N, device, P, st);
+    default: return launch_static<6>(N, device, P, st);
   }
 }
 
@@ -208,6 +268,39 @@ int urgym_step(urgym_handle h, const real* action_dev, const real* u_dev, const 
   KParams R; std::memset(&R, 0, sizeof(R));
   R.mode = MODE_RESET; R.mask = h->d_defer; R.draws = draws_dev; R.obs = obs_dev; R.nticks = nticks_dev; R.deferred_pass = 1;
   return launch(h, R, stream);
+}
+
+int urgym_step_static(int env_type, int device, int num_envs, uint64_t seed, int env_index_offset, int reward_sparse,
+                      const real* state_in_dev, const real* action_dev, const real* u_dev, const real* draws_dev, real* state_out_dev,
+                      real* obs_dev, real* reward_dev, uint8_t* terminated_dev, uint8_t* truncated_dev, uint8_t* success_dev,
+                      real* final_obs_dev, int32_t* nticks_dev, double* stats_dev, int autoreset, void* stream) {
+  if (env_type < 0 || env_type >= UG_ENV_COUNT || num_envs <= 0) return fail(URGYM_E_ARG, "urgym_step_static: bad env type or env count");
+  if (num_envs > UG_STATIC_MAX_ENVS)
+    return fail(URGYM_E_ARG, "urgym_step_static: num_envs " + std::to_string(num_envs) + " exceeds URGYM_STATIC_MAX_ENVS (" +
+                             std::to_string(UG_STATIC_MAX_ENVS) + "), the size of the library's static scratch; split the batch or use urgym_step");
+  if (!state_in_dev || !state_out_dev || !action_dev || !obs_dev || !reward_dev || !terminated_dev || !truncated_dev || !success_dev)
+    return fail(URGYM_E_ARG, "urgym_step_static: null argument");
+  StaticScratch* sc; { int rc = static_setup(device, &sc); if (rc) return rc; }
+  cudaStream_t st = (cudaStream_t)stream;
+  if (state_out_dev != state_in_dev)
+    CK(cudaMemcpyAsync(state_out_dev, state_in_dev, (size_t)num_envs * UG_STATE * sizeof(real), cudaMemcpyDeviceToDevice, st));
+  CK(cudaMemsetAsync(sc->stats, 0, sizeof(sc->stats), st));   // the counters accumulate by atomics: they must start at zero
+  const bool split = autoreset && default_split_reset(env_type);
+  KParams P; std::memset(&P, 0, sizeof(P));
+  P.model = &sc->model[env_type]; P.state = state_out_dev; P.N = num_envs; P.stats = sc->stats;
+  P.seed = seed; P.gidx0 = env_index_offset; P.sparse = reward_sparse;
+  P.mode = MODE_STEP; P.action = action_dev; P.u = u_dev; P.draws = draws_dev; P.obs = obs_dev; P.reward = reward_dev;
+  P.term = terminated_dev; P.trunc = truncated_dev; P.succ = success_dev; P.final_obs = final_obs_dev; P.nticks = nticks_dev; P.autoreset = autoreset;
+  if (split) P.defer = sc->defer;
+  { int rc = launch_static_any(env_type, num_envs, device, P, st); if (rc) return rc; }
+  if (split) {   // same scheduling as urgym_step: the finished envs restart in a reset-only grid
+    KParams R = P;
+    R.mode = MODE_RESET; R.mask = sc->defer; R.defer = nullptr; R.deferred_pass = 1;
+    R.action = nullptr; R.u = nullptr; R.reward = nullptr; R.term = nullptr; R.trunc = nullptr; R.succ = nullptr; R.final_obs = nullptr; R.autoreset = 0;
+    int rc = launch_static_any(env_type, num_envs, device, R, st); if (rc) return rc;
+  }
+  if (stats_dev) CK(cudaMemcpyAsync(stats_dev, sc->stats, sizeof(sc->stats), cudaMemcpyDeviceToDevice, st));
+  return URGYM_OK;
 }
 
 int urgym_step_logic(urgym_handle h, const real* action_dev, const real* u_dev, const int32_t* pairs_dev, const int32_t* count_dev,
