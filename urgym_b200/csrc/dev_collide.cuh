@@ -281,6 +281,172 @@ __device__ __noinline__ int poly_box(const DevPoly& P, f3 o, const m3& R, const 
   return cnt;
 }
 
+// ---------------------------------------------------------------------------------------------------------------
+// poly_box by four lanes. A tick of the ball / golf scenes runs 4..10 polytope pairs (finger links against the paddle or
+// the club), each 4.5 k instructions of separating-axis tests plus the clipping when one lane does it, with its vertex and
+// clip buffers in local memory: measured 190 k cycles per tick with one warp per SM and 600 k with thirteen (the buffers
+// fall out of the small L1 next to 225 KB of shared memory), i.e. more than the PGS sweeps (profiles/r02_latency_chains.txt).
+// Here the four lanes [4g, 4g + 4) of the warp take one pair: each computes every fourth axis separation (the same
+// expressions as poly_box, operand for operand) into a shared-memory table, then all four scan the table in poly_box's
+// order with poly_box's comparisons, so the selected axis is the one poly_box selects; lane 4g clips in shared memory.
+// Buffers: `sc` = UG_PB_SCRATCH reals of shared memory per group: [0,48) world vertices, later the result (count is the
+// return value; 4 x {posA, posB, n, dist}); [48,192) two clip buffers of 24 vertices, during the axis tests the table of
+// separations [48,122) and of edge-direction signs [122,158); [192,208) the kept distances.
+#define UG_PB_SCRATCH 208
+#define UG_PB_GROUPS 8
+UG_DEV int clip_halfspace_sm(const real* src, int n, f3 o, f3 m, real* dst) {
+  int k = 0;
+  for (int i = 0; i < n; i++) {
+    const f3 P = ld3(src + 3 * i), Q = ld3(src + 3 * ((i + 1 == n) ? 0 : i + 1));
+    const real dp = dot(m, P - o), dq = dot(m, Q - o);
+    if (dp >= 0._r) { st3(dst + 3 * k, P); k++; }
+    if ((dp >= 0._r) != (dq >= 0._r)) { const real t = dp / (dp - dq); st3(dst + 3 * k, P + (Q - P) * t); k++; }
+  }
+  return k > 16 ? 16 : k;
+}
+
+__device__ __noinline__ int poly_box_coop(const DevPoly& P, f3 o, const m3& R, const BoxW& B, real margin, real* sc, int sub, unsigned gmask) {
+  real* const vs = sc; real* const sep = sc + 48; real* const sgnf = sc + 122; real* const dist = sc + 192;
+  const int nv = P.nv, nf = P.nf, ne = P.ne;
+#pragma unroll 1
+  for (int i = sub; i < nv; i += 4) st3(vs + 3 * i, o + mulv(R, ld3(P.v[i])));
+  const f3 bax[3] = {col(B.R, 0), col(B.R, 1), col(B.R, 2)};
+  __syncwarp(gmask);
+  // ---- the table of separations: [0,nf) polytope faces, [nf,nf+6) box faces (+, - per axis), [nf+6, nf+6+3ne) edge pairs
+#pragma unroll 1
+  for (int f = sub; f < nf; f += 4) {
+    const f3 n = mulv(R, ld3(P.fn[f]));
+    const real fd = P.fn[f][3] + dot(n, o);
+    const real sB = dot(n, B.c) - (B.h.x * rabs(dot(n, bax[0])) + B.h.y * rabs(dot(n, bax[1])) + B.h.z * rabs(dot(n, bax[2])));
+    sep[f] = sB - fd;
+  }
+  if (sub < 3) {
+    const int j = sub;
+    const f3 bj = j == 0 ? bax[0] : (j == 1 ? bax[1] : bax[2]);
+    real lo = 1e30_r, hi = -1e30_r;
+#pragma unroll 1
+    for (int i = 0; i < nv; i++) { real p = dot(bj, ld3(vs + 3 * i) - B.c); lo = rmin(lo, p); hi = rmax(hi, p); }
+    const real hj = comp(B.h, j);
+    sep[nf + 2 * j] = lo - hj; sep[nf + 2 * j + 1] = -hi - hj;
+  }
+#pragma unroll 1
+  for (int t = sub; t < 3 * ne; t += 4) {
+    const int e = t / 3, j = t - 3 * e;
+    const f3 ed = mulv(R, ld3(P.ed[e]));
+    const f3 bj = j == 0 ? bax[0] : (j == 1 ? bax[1] : bax[2]);
+    f3 L = cross(ed, bj); const real l = norm3(L);
+    real sx = -1e30_r, fl = 0._r;            // degenerate pair of directions: never separating, never selected
+    if (!(l <= 1e-9_r)) {
+      L = L * (1.0_r / l);
+      real mnA = 1e30_r, mxA = -1e30_r;
+#pragma unroll 1
+      for (int i = 0; i < nv; i++) { real p = dot(L, ld3(vs + 3 * i) - B.c); mnA = rmin(mnA, p); mxA = rmax(mxA, p); }
+      const real rB = B.h.x * rabs(dot(L, bax[0])) + B.h.y * rabs(dot(L, bax[1])) + B.h.z * rabs(dot(L, bax[2]));
+      const real s1 = mnA - rB, s2 = -mxA - rB;
+      sx = rmax(s1, s2); fl = s1 >= s2 ? 1._r : 0._r;
+    }
+    sep[nf + 6 + t] = sx; sgnf[t] = fl;
+  }
+  __syncwarp(gmask);
+  // ---- every lane scans the table in poly_box's order
+  real best = -1e30_r; int kind = 0, idx = 0, sgn = 1, tsel = 0;
+#pragma unroll 1
+  for (int f = 0; f < nf; f++) { const real sv = sep[f]; if (sv > margin) return 0; if (sv > best) { best = sv; kind = 0; idx = f; } }
+#pragma unroll 1
+  for (int c = 0; c < 6; c++) { const real sv = sep[nf + c]; if (sv > margin) return 0; if (sv > best) { best = sv; kind = 1; idx = c >> 1; sgn = (c & 1) ? -1 : 1; } }
+#pragma unroll 1
+  for (int t = 0; t < 3 * ne; t++) { const real sv = sep[nf + 6 + t]; if (sv > margin) return 0; if (edge_bias(sv) > best) { best = sv; kind = 2; tsel = t; } }
+  const real sel_flag = sgnf[tsel];
+  // kind 1 needs the polytope's face most against the reference face: same split, table in sep[0,nf)
+  f3 rn = mk3(0, 0, 1);
+  if (kind == 1) rn = (idx == 0 ? bax[0] : (idx == 1 ? bax[1] : bax[2])) * (real)sgn;
+  __syncwarp(gmask);                         // everyone has read the table
+  if (kind == 1) {
+#pragma unroll 1
+    for (int f = sub; f < nf; f += 4) sep[f] = dot(mulv(R, ld3(P.fn[f])), rn);
+  }
+  __syncwarp(gmask);
+  int cnt = 0;
+  if (sub == 0) {
+    real* const res = vs;                    // the vertices are dead once the clip has read them (kind 0 reads them; see below)
+    if (kind == 2) {                         // one point: closest points of the two supporting edges
+      const int ea = tsel / 3, eb = tsel - 3 * ea;
+      f3 L = cross(mulv(R, ld3(P.ed[ea])), eb == 0 ? bax[0] : (eb == 1 ? bax[1] : bax[2]));
+      L = L * (1.0_r / norm3(L));
+      const f3 nBA = sel_flag != 0._r ? L : -L;
+      real exA = 1e30_r;
+      for (int i = 0; i < nv; i++) exA = rmin(exA, dot(nBA, ld3(vs + 3 * i)));
+      f3 pa = mk3(0, 0, 0); int ca = 0;
+      for (int i = 0; i < nv; i++) if (dot(nBA, ld3(vs + 3 * i)) <= exA + 1e-5_r) { pa = pa + ld3(vs + 3 * i); ca++; }
+      pa = pa * (1.0_r / (real)ca);
+      f3 pb = B.c;
+#pragma unroll
+      for (int k = 0; k < 3; k++) if (k != eb) pb = pb + bax[k] * ((dot(nBA, bax[k]) > 0._r ? 1.0_r : -1.0_r) * comp(B.h, k));
+      const f3 ua = mulv(R, ld3(P.ed[ea])), ub = eb == 0 ? bax[0] : (eb == 1 ? bax[1] : bax[2]), d = pb - pa;
+      const real uaub = dot(ua, ub), q1 = dot(ua, d), q2 = -dot(ub, d), den = 1.0_r - uaub * uaub;
+      real beta = 0._r;
+      if (den > 1e-4_r) beta = (uaub * q1 + q2) / den;
+      pb = pb + ub * beta;
+      st3(res + 0, pb + nBA * best); st3(res + 3, pb); st3(res + 6, nBA); res[9] = best;
+      cnt = 1;
+    } else {
+      real* bufA = sc + 48; real* bufB = sc + 120;
+      int n = 0; real rd; f3 nBA;
+      if (kind == 0) {                       // reference face on the polytope; incident = the box face most against it
+        rn = mulv(R, ld3(P.fn[idx])); rd = P.fn[idx][3] + dot(rn, o); nBA = -rn;
+        int la = 0; real lav = -1._r;
+#pragma unroll
+        for (int j = 0; j < 3; j++) { real t = rabs(dot(rn, bax[j])); if (t > lav) { lav = t; la = j; } }
+        const int a1 = (la + 1) % 3, a2 = (la + 2) % 3;
+        const f3 bl = la == 0 ? bax[0] : (la == 1 ? bax[1] : bax[2]), b1 = a1 == 0 ? bax[0] : (a1 == 1 ? bax[1] : bax[2]), b2 = a2 == 0 ? bax[0] : (a2 == 1 ? bax[1] : bax[2]);
+        const real sg = dot(rn, bl) > 0._r ? -1.0_r : 1.0_r;
+        const f3 fc = B.c + bl * (sg * comp(B.h, la)), e1 = b1 * comp(B.h, a1), e2 = b2 * comp(B.h, a2);
+        st3(bufA + 0, fc - e1 - e2); st3(bufA + 3, fc + e1 - e2); st3(bufA + 6, fc + e1 + e2); st3(bufA + 9, fc - e1 + e2); n = 4;
+        const int fcnt = P.fcount[idx];
+        for (int k = 0; k < fcnt && n > 0; k++) {
+          const f3 a = ld3(vs + 3 * P.floop[idx][k]), e = ld3(vs + 3 * P.floop[idx][(k + 1 == fcnt) ? 0 : k + 1]) - a;
+          n = clip_halfspace_sm(bufA, n, a, cross(rn, e), bufB);
+          real* t = bufA; bufA = bufB; bufB = t;
+        }
+      } else {                               // reference face on the box; incident = the polytope's face most against it
+        nBA = rn; rd = dot(rn, B.c) + comp(B.h, idx);
+        int fi = 0; real fv = 1e30_r;
+#pragma unroll 1
+        for (int f = 0; f < nf; f++) { const real t = sep[f]; if (t < fv) { fv = t; fi = f; } }
+        const int fcnt = P.fcount[fi];
+        real* inc = sc + 120;                // the table still occupies [48, 48 + nf): load the face into the other buffer
+        for (int k = 0; k < fcnt; k++) st3(inc + 3 * k, ld3(vs + 3 * P.floop[fi][k]));
+        n = fcnt; bufA = sc + 120; bufB = sc + 48;
+        const int c1 = (idx + 1) % 3, c2 = (idx + 2) % 3;
+        for (int t = 0; t < 4 && n > 0; t++) {
+          const int c = t < 2 ? c1 : c2;
+          const f3 ax = (c == 0 ? bax[0] : (c == 1 ? bax[1] : bax[2])) * ((t & 1) ? -1.0_r : 1.0_r);
+          n = clip_halfspace_sm(bufA, n, B.c + ax * comp(B.h, c), -ax, bufB);
+          real* tt = bufA; bufA = bufB; bufB = tt;
+        }
+      }
+      int m = 0;
+      for (int i = 0; i < n; i++) {
+        const f3 pt = ld3(bufA + 3 * i);
+        const real dv = dot(rn, pt) - rd;
+        if (dv <= margin) { st3(bufA + 3 * m, pt); dist[m] = dv; m++; }
+      }
+      if (m > 0) {
+        cnt = m < 4 ? m : 4; int i0 = 0;
+        if (m > 4) for (int t = 1; t < m; t++) if (-dist[t] > -dist[i0]) i0 = t;
+        for (int j = 0; j < cnt; j++) {
+          const int sl = m > 4 ? (i0 + (j * m) / 4) % m : j;
+          const f3 pt = ld3(bufA + 3 * sl); const real dv = dist[sl];
+          real* r = res + 10 * j;
+          if (kind == 0) { st3(r, pt + nBA * dv); st3(r + 3, pt); } else { st3(r, pt); st3(r + 3, pt - nBA * dv); }
+          st3(r + 6, nBA); r[9] = dv;
+        }
+      }
+    }
+  }
+  return cnt;
+}
+
 // Closest point of the polytope to a sphere centre, like sphere_box: point on the polytope, normal towards the sphere.
 __device__ __noinline__ bool sphere_poly(f3 sc, real r, const DevPoly& P, f3 o, const m3& R, real margin, f3& on_poly, f3& n_ps, real& dist) {
   const int nf = P.nf;

@@ -104,8 +104,11 @@ __device__ __noinline__ void collide(S& s, const DevModel& M, const Gp<G> gp) {
         }
       }
     }
-    // robot links with mesh geometry whose bounding box is close: the polytope itself decides (few lanes, rarely)
-    if (n > 0 && M.shapes[sa].kind == 2) {
+    // robot links with mesh geometry whose bounding box is close: the polytope itself decides. Against a sphere that is
+    // cheap and stays in the pair's lane; against a box the pairs are handed to groups of four lanes (poly_box_coop),
+    // eight pairs at a time, through scratch in the idle solver block behind the near list.
+    const bool is_poly = n > 0 && M.shapes[sa].kind == 2;
+    if (is_poly && M.shapes[sb].kind != 0) {
       const DevShape& A = M.shapes[sa]; const DevShape& B = M.shapes[sb];
       const real margin = rmin(A.cbt, B.cbt);
       const int lb = M.link_body[A.link];
@@ -113,11 +116,52 @@ __device__ __noinline__ void collide(S& s, const DevModel& M, const Gp<G> gp) {
       const f3 o = ld3(s.bp[lb]) + mulv(Rb, ld3(M.link_lpos[A.link]));
       const m3 Rl = mulm(Rb, ldm(M.link_lrot[A.link]));
       BoxW b; shape_box(s, B, b);
-      if (B.kind == 0) n = poly_box(M.polys[A.poly], o, Rl, b, margin, pts);
-      else {
-        f3 oa, na; real d; n = 0;
-        if (sphere_poly(b.c, B.radius, M.polys[A.poly], o, Rl, margin, oa, na, d)) { pts[0].n = -na; pts[0].dist = d; pts[0].posA = oa; pts[0].posB = oa + na * d; n = 1; }
+      f3 oa, na; real d; n = 0;
+      if (sphere_poly(b.c, B.radius, M.polys[A.poly], o, Rl, margin, oa, na, d)) { pts[0].n = -na; pts[0].dist = d; pts[0].posA = oa; pts[0].posB = oa + na * d; n = 1; }
+    }
+    if constexpr (G == 32) {
+      const bool job = is_poly && M.shapes[sb].kind == 0;
+      const unsigned jm = gp.ballot(job);
+      const int njobs = __popc(jm), jidx = __popc(jm & ((1u << l) - 1u));
+      real* const scratch = s.u.T + 64;           // the near list holds UG_MAXPAIRS bytes at the start of T
+      static_assert(64 + UG_PB_GROUPS * UG_PB_SCRATCH <= S::TTRI, "polytope scratch does not fit the idle solver block");
+#pragma unroll 1
+      for (int j0 = 0; j0 < njobs; j0 += UG_PB_GROUPS) {
+        const int g = l >> 2, sub = l & 3, myjob = j0 + g;
+        const bool active = myjob < njobs;
+        const int owner = active ? (int)__fns(jm, 0, myjob + 1) : 0;
+        const int pj = gp.shfl(p, owner);
+        real* const sc = scratch + UG_PB_SCRATCH * g;
+        int cnt = 0;
+        if (active) {
+          const DevShape& A = M.shapes[M.pairs[pj][0]]; const DevShape& B = M.shapes[M.pairs[pj][1]];
+          const real margin = rmin(A.cbt, B.cbt);
+          const int lb = M.link_body[A.link];
+          const m3 Rb = ldm(s.bR[lb]);
+          const f3 o = ld3(s.bp[lb]) + mulv(Rb, ld3(M.link_lpos[A.link]));
+          const m3 Rl = mulm(Rb, ldm(M.link_lrot[A.link]));
+          BoxW b; shape_box(s, B, b);
+          cnt = poly_box_coop(M.polys[A.poly], o, Rl, b, margin, sc, sub, 0xFu << (l & ~3));
+        }
+        gp.sync();
+        const bool mine = job && jidx >= j0 && jidx < j0 + UG_PB_GROUPS;
+        const int got = gp.shfl(cnt, mine ? 4 * (jidx - j0) : 0);
+        if (mine) {
+          n = got;
+          const real* r = scratch + UG_PB_SCRATCH * (jidx - j0);
+          for (int i = 0; i < got; i++) { pts[i].posA = ld3(r + 10 * i); pts[i].posB = ld3(r + 10 * i + 3); pts[i].n = ld3(r + 10 * i + 6); pts[i].dist = r[10 * i + 9]; }
+        }
+        gp.sync();
       }
+    } else if (is_poly && M.shapes[sb].kind == 0) {
+      const DevShape& A = M.shapes[sa]; const DevShape& B = M.shapes[sb];
+      const real margin = rmin(A.cbt, B.cbt);
+      const int lb = M.link_body[A.link];
+      const m3 Rb = ldm(s.bR[lb]);
+      const f3 o = ld3(s.bp[lb]) + mulv(Rb, ld3(M.link_lpos[A.link]));
+      const m3 Rl = mulm(Rb, ldm(M.link_lrot[A.link]));
+      BoxW b; shape_box(s, B, b);
+      n = poly_box(M.polys[A.poly], o, Rl, b, margin, pts);
     }
     int incl = n;
 #pragma unroll
