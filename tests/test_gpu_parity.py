@@ -593,7 +593,9 @@ def test_shipped_actors_on_the_device_match_the_oracle_replay(name):
     got = R.rollout_cuda(name, 10000, seed=123)
     m = dict(env=name, device=got, oracle=want, pybullet=json.load(open(ORACLE_REPLAY))[name]['pybullet_training_last_100'])
     _record('actor_replay', m)
-    assert got['capacity_overflow_ticks'] / max(got['mean_length'] * got['episodes'], 1) < 0.05, m
+    # ticks that carried more manifold points than the kernel keeps, under the trained policies (which work with the fingers on
+    # the table, next to the cubes): measured 0.2 % of the ticks for CubesPush, below 2 % everywhere
+    assert got['capacity_overflow_ticks'] / max(got['ticks'], 1) < 0.02, m
     for key in ('return', 'length', 'success'):
         a, b_ = got['mean_%s' % key if key != 'success' else 'success_rate'], want['mean_%s' % key if key != 'success' else 'success_rate']
         se = np.hypot(got['se_%s' % key], want['se_%s' % key])

@@ -77,7 +77,8 @@ def rollout_cuda(name, episodes, seed=123, precision='f32'):
         succ |= su.bool() & alive
         alive &= ~(term.bool() | trunc.bool())
     out = summarize(ret.cpu().numpy(), length.cpu().numpy(), succ.cpu().numpy())
-    out['capacity_overflow_ticks'] = b.stats()['capacity_overflow_ticks']
+    st = b.stats()
+    out['capacity_overflow_ticks'] = st['capacity_overflow_ticks']; out['ticks'] = st['ticks']
     b.close()
     return out
 

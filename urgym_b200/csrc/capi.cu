@@ -69,10 +69,14 @@ int group_size() { return 32; }
 // Whether auto-resets run in a launch of their own. Measured per env type (profiles/r01_reset_scheduling.txt): the
 // ball scenes gain 7-19% because step ticks and the robot-only ticks of a reset no longer share an SM, the scenes whose
 // reset settles for hundreds of ticks (Golf) lose to the latency of a thin second grid. URGYM_SPLIT_RESET=0/1 overrides.
-bool default_split_reset(int env_type) {
+// Round 2 (profiles/r02_split_vs_fused.txt): with the polytope gripper the ball stays on the paddle four times longer, so only
+// ~5 % of the envs restart per step; at <= 4096 envs per GPU the step is then bound by the serial chain (step ticks + 162
+// reset ticks of the slowest env) and the fused launch, which starts every reset the moment its env finishes, is 0-3 % ahead;
+// from 8192 envs on the launch is throughput-bound and the split form wins by 6-20 %.
+bool default_split_reset(int env_type, int num_envs) {
   static const bool dflt[UG_ENV_COUNT] = {true, true, false, false, false, false, false};
   const char* e = getenv("URGYM_SPLIT_RESET");
-  return e ? atoi(e) != 0 : dflt[env_type];
+  return e ? atoi(e) != 0 : (dflt[env_type] && num_envs > 4096);
 }
 
 template <int ENV, int G>
@@ -205,7 +209,7 @@ int urgym_create(int env_type, int num_envs, int device, uint64_t seed, int env_
   if (getenv("URGYM_STACK")) CK(cudaDeviceSetLimit(cudaLimitStackSize, (size_t)atoi(getenv("URGYM_STACK"))));
   urgym_handle h = new urgym_env_s;
   h->env_type = env_type; h->N = num_envs; h->device = device; h->seed = seed; h->gidx0 = env_index_offset; h->sparse = reward_sparse;
-  h->split_reset = default_split_reset(env_type);
+  h->split_reset = default_split_reset(env_type, num_envs);
   if (build_model(env_type, &h->hmodel)) { delete h; return fail(URGYM_E_ARG, "model build failed"); }
   { const char* e = getenv("URGYM_GENERIC_SWEEPS"); h->hmodel.generic_sweeps = e && atoi(e) != 0; }
   size_t n = (size_t)num_envs; int od = h->hmodel.obs_dim, ad = h->hmodel.act_dim;
@@ -285,7 +289,7 @@ int urgym_step_static(int env_type, int device, int num_envs, uint64_t seed, int
   if (state_out_dev != state_in_dev)
     CK(cudaMemcpyAsync(state_out_dev, state_in_dev, (size_t)num_envs * UG_STATE * sizeof(real), cudaMemcpyDeviceToDevice, st));
   CK(cudaMemsetAsync(sc->stats, 0, sizeof(sc->stats), st));   // the counters accumulate by atomics: they must start at zero
-  const bool split = autoreset && default_split_reset(env_type);
+  const bool split = autoreset && default_split_reset(env_type, num_envs);
   KParams P; std::memset(&P, 0, sizeof(P));
   P.model = &sc->model[env_type]; P.state = state_out_dev; P.N = num_envs; P.stats = sc->stats;
   P.seed = seed; P.gidx0 = env_index_offset; P.sparse = reward_sparse;

@@ -10,7 +10,8 @@ struct CPt { f3 posA, posB, n; real dist; };  // n from B to A
 
 UG_DEV real edge_bias(real s) { return s < 0._r ? s * 1.05_r : s / 1.05_r; }
 
-// Sutherland-Hodgman clip of a convex polygon (x,y,z per vertex) against |x|<=hx, |y|<=hy. Buffers hold 16 vertices.
+// Sutherland-Hodgman clip of a convex polygon (x,y,z per vertex) against |x|<=hx, |y|<=hy. The callers clip a quad: each of
+// the four half-planes adds at most one vertex, so the buffers hold 8 vertices (local memory: keep it small).
 __device__ __noinline__ int clip_rect(real (*bufA)[3], int n, real hx, real hy, real (*bufB)[3], int* which) {
   real (*src)[3] = bufA; real (*dst)[3] = bufB;
   int flip = 0;
@@ -106,7 +107,7 @@ __device__ __noinline__ int box_box(const BoxW& A, const BoxW& B, real margin, C
   f3 fc = inc.c + col(inc.R, la) * (sg * comp(inc.h, la)) - ref.c;
   f3 e1v = col(inc.R, a1) * comp(inc.h, a1), e2v = col(inc.R, a2) * comp(inc.h, a2);
   f3 rc1 = col(ref.R, c1), rc2 = col(ref.R, c2);
-  real bufA[16][3], bufB[16][3];
+  real bufA[8][3], bufB[8][3];
   {
     f3 quad[4] = {fc - e1v - e2v, fc + e1v - e2v, fc + e1v + e2v, fc - e1v + e2v};
 #pragma unroll
@@ -115,7 +116,7 @@ __device__ __noinline__ int box_box(const BoxW& A, const BoxW& B, real margin, C
   int which;
   int n = clip_rect(bufA, 4, comp(ref.h, c1), comp(ref.h, c2), bufB, &which);
   real (*cl)[3] = which ? bufB : bufA;
-  int keep[16]; real dep[16]; int m = 0;
+  int keep[8]; real dep[8]; int m = 0;
   real hk = comp(ref.h, k);
   for (int v = 0; v < n; v++) { real dv = hk - cl[v][2]; if (dv >= -margin) { keep[m] = v; dep[m] = dv; m++; } }
   if (m == 0) return 0;

@@ -472,9 +472,9 @@ __device__ __noinline__ real solve_and_integrate(S& s, const DevModel& M, const 
   const unsigned aEc = aE + UG_RB * (unsigned)((UG_NCOL + l) * UG_NCOL);  // contact slot o: + o * G * UG_NCOL * 4
   // T(r, c) for the lane's row c = l + G o of contact slot o: c <= r -> aTrow[o] + tri(r), c > r -> aTcol[o] + r (in scalars).
   // Lanes beyond the last row address the last row (their operand is never used).
-  unsigned aTrow[NSC], aTcol[NSC];
+  unsigned aTrow[NSC], aTcol[NSC]; int cown[NSC];
 #pragma unroll
-  for (int o = 0; o < NSC; o++) { const int c_ = min(l + G * o, RC - 1); aTrow[o] = aT + UG_RB * (unsigned)c_; aTcol[o] = aT + UG_RB * (unsigned)((c_ * (c_ + 1)) / 2); }
+  for (int o = 0; o < NSC; o++) { const int c_ = min(l + G * o, RC - 1); cown[o] = c_; aTrow[o] = aT + UG_RB * (unsigned)c_; aTcol[o] = aT + UG_RB * (unsigned)((c_ * (c_ + 1)) / 2); }
   real limv[NSC];
 #pragma unroll
   for (int so = 0; so < NSC; so++) limv[so] = 0._r;
@@ -500,20 +500,47 @@ __device__ __noinline__ real solve_and_integrate(S& s, const DevModel& M, const 
     _Pragma("unroll") for (int k_ = 0; k_ < NSJ; k_++) w[k_] = rfma(ej_[k_], delta, w[k_]);              \
     _Pragma("unroll") for (int o_ = 0; o_ < (NACT); o_++) w[NSJ + o_] = rfma(ec_[o_], delta, w[NSJ + o_]); \
   }
-  // operands of a contact-row step (rows ROW and, when PAIR, ROW + 1): E entries for the joint slots, T entries for
-  // the contact slots
-  // SO = the (compile-time) contact slot of the stepping row: slots below it hold only rows c < ROW, slots above only c > ROW
-#define UG_T_ADDR(o_, SO, ROW, TRI) ((o_) < (SO) ? aTrow[o_] + (TRI) : ((o_) > (SO) ? aTcol[o_] + UG_RB * (unsigned)(ROW) : \
-                                     ((l + G * (o_)) <= (ROW) ? aTrow[o_] + (TRI) : aTcol[o_] + UG_RB * (unsigned)(ROW))))
-#define UG_CONTACT_LOAD(ROW, SO, PAIR, NACT)                                                             \
-    const unsigned er_ = UG_RB * (unsigned)((ROW) * UG_NCOL);                                           \
-    const unsigned t0_ = UG_RB * (unsigned)(((ROW) * ((ROW) + 1)) >> 1), t1_ = t0_ + UG_RB * (unsigned)((ROW) + 1); \
+  // Operands of a contact-row step: E entries for the joint slots, T entries for the contact slots. Each operand has ONE
+  // running shared-memory address per lane: the E entry of the lane's column advances by a row of E per stepping row; the T
+  // entry of the lane's own row c against stepping row r sits at tri(r) + c for c <= r and at tri(c) + r for c > r, so going
+  // from r to r + 1 it advances by one scalar while r < c and by r + 1 scalars from there on (the crossing r = c - 1 -> c is one
+  // scalar too). Slots below the stepping slot SO hold only rows c < r and slots above it only rows c > r, so only the
+  // stepping slot needs the compare. (Round 1-2a recomputed tri(r), two candidate addresses and a select per operand per
+  // step: 13-18 integer instructions of the 27 / 47 of a normal / friction step; profiles/r02_ncu_full_*.)
+  //   UG_TP_INIT: addresses for stepping row R0. UG_ROW_LOAD / UG_PAIR_LOAD: load the operands of row ROW (and ROW + 1) and
+  //   advance to ROW + 1 (ROW + 2); RB1 = UG_RB * (ROW + 1).
+#define UG_TP_INIT(SO, R0, NACT)                                                                         \
+    {                                                                                                    \
+      const unsigned tri0_ = UG_RB * (unsigned)(((R0) * ((R0) + 1)) >> 1), rb0_ = UG_RB * (unsigned)(R0); \
+      _Pragma("unroll") for (int k_ = 0; k_ < NSJ; k_++) pE[k_] = aEq[k_] + (UG_RB * UG_NCOL) * (unsigned)(R0); \
+      _Pragma("unroll") for (int o_ = 0; o_ < (NACT); o_++)                                              \
+        pT[o_] = (o_) < (SO) ? aTrow[o_] + tri0_ : ((o_) > (SO) ? aTcol[o_] + rb0_ : (cown[o_] <= (R0) ? aTrow[o_] + tri0_ : aTcol[o_] + rb0_)); \
+    }
+#define UG_ROW_LOAD(SO, ROW, RB1, NACT)                                                                  \
+    real uj_[NSJ], uc_[NACT];                                                                           \
+    _Pragma("unroll") for (int k_ = 0; k_ < NSJ; k_++) { uj_[k_] = lds(pE[k_]); pE[k_] += UG_RB * UG_NCOL; } \
+    _Pragma("unroll") for (int o_ = 0; o_ < (NACT); o_++) {                                              \
+      uc_[o_] = lds(pT[o_]);                                                                             \
+      pT[o_] += (o_) < (SO) ? (RB1) : ((o_) > (SO) ? UG_RB : ((ROW) < cown[o_] ? UG_RB : (RB1)));        \
+    }
+#define UG_PAIR_LOAD(SO, ROW, RB1, NACT)                                                                 \
     real uj_[NSJ], vj_[NSJ], uc_[NACT], vc_[NACT];                                                      \
-    _Pragma("unroll") for (int k_ = 0; k_ < NSJ; k_++) { uj_[k_] = lds(aEq[k_] + er_); vj_[k_] = (PAIR) ? lds(aEq[k_] + er_ + UG_RB * UG_NCOL) : 0._r; } \
-    _Pragma("unroll") for (int o_ = 0; o_ < (NACT); o_++) { uc_[o_] = lds(UG_T_ADDR(o_, SO, ROW, t0_)); vc_[o_] = (PAIR) ? lds(UG_T_ADDR(o_, SO, (ROW) + 1, t1_)) : 0._r; }
-#define UG_CONTACT_APPLY(DA, DB, PAIR, NACT)                                                             \
-    _Pragma("unroll") for (int k_ = 0; k_ < NSJ; k_++) { w[k_] = rfma(uj_[k_], DA, w[k_]); if (PAIR) w[k_] = rfma(vj_[k_], DB, w[k_]); } \
-    _Pragma("unroll") for (int o_ = 0; o_ < (NACT); o_++) { w[NSJ + o_] = rfma(uc_[o_], DA, w[NSJ + o_]); if (PAIR) w[NSJ + o_] = rfma(vc_[o_], DB, w[NSJ + o_]); }
+    _Pragma("unroll") for (int k_ = 0; k_ < NSJ; k_++) { uj_[k_] = lds(pE[k_]); vj_[k_] = lds(pE[k_] + UG_RB * UG_NCOL); pE[k_] += 2u * UG_RB * UG_NCOL; } \
+    _Pragma("unroll") for (int o_ = 0; o_ < (NACT); o_++) {                                              \
+      uc_[o_] = lds(pT[o_]);                                                                             \
+      if ((o_) > (SO)) { vc_[o_] = lds(pT[o_] + UG_RB); pT[o_] += 2u * UG_RB; }                          \
+      else {                                                                                             \
+        const unsigned q_ = pT[o_] + ((o_) < (SO) ? (RB1) : ((ROW) < cown[o_] ? UG_RB : (RB1)));         \
+        vc_[o_] = lds(q_);                                                                               \
+        pT[o_] = q_ + ((o_) < (SO) ? (RB1) + UG_RB : ((ROW) + 1 < cown[o_] ? UG_RB : (RB1) + UG_RB));    \
+      }                                                                                                  \
+    }
+#define UG_ROW_APPLY(DA, NACT)                                                                           \
+    _Pragma("unroll") for (int k_ = 0; k_ < NSJ; k_++) w[k_] = rfma(uj_[k_], DA, w[k_]);                 \
+    _Pragma("unroll") for (int o_ = 0; o_ < (NACT); o_++) w[NSJ + o_] = rfma(uc_[o_], DA, w[NSJ + o_]);
+#define UG_PAIR_APPLY(DA, DB, NACT)                                                                      \
+    _Pragma("unroll") for (int k_ = 0; k_ < NSJ; k_++) { w[k_] = rfma(uj_[k_], DA, w[k_]); w[k_] = rfma(vj_[k_], DB, w[k_]); } \
+    _Pragma("unroll") for (int o_ = 0; o_ < (NACT); o_++) { w[NSJ + o_] = rfma(uc_[o_], DA, w[NSJ + o_]); w[NSJ + o_] = rfma(vc_[o_], DB, w[NSJ + o_]); }
   // joint rows, order alternates with the iteration parity (backward on even sweeps)
 #define UG_JOINT_SWEEP(NACT)                                                                             \
   /* a lane's impulse changes only at its own step, so its clamp bounds are constant over the sweep */  \
@@ -540,49 +567,62 @@ __device__ __noinline__ real solve_and_integrate(S& s, const DevModel& M, const 
   // implicit cone
 #define UG_CONTACT_SWEEP(NACT)                                                                           \
   {                                                                                                      \
+    unsigned pE[NSJ], pT[NACT];                                                                          \
     const real nlo = lo[NSJ] - lam[NSJ], nhi = hi[NSJ] - lam[NSJ];   /* constant over the sweep, as above */ \
-    _Pragma("unroll 1") for (int row = 0; row < NC; row++) {                                             \
-      UG_CONTACT_LOAD(row, 0, false, NACT)                                                               \
-      real d_ = rfma(-w[NSJ], invd[NSJ], rhs[NSJ]);                                                     \
-      d_ = rmin(rmax(d_, nlo), nhi);                                                                   \
-      const real delta = gp.shfl(d_, row);                                                              \
-      if (l == row) lam[NSJ] += delta;                                                                   \
-      UG_CONTACT_APPLY(delta, 0._r, false, NACT)                                                          \
+    UG_TP_INIT(0, 0, NACT)                                                                               \
+    {                                                                                                    \
+      unsigned rb1 = UG_RB;                                                                              \
+      _Pragma("unroll 1") for (int row = 0; row < NC; row++, rb1 += UG_RB) {                             \
+        UG_ROW_LOAD(0, row, rb1, NACT)                                                                   \
+        real d_ = rfma(-w[NSJ], invd[NSJ], rhs[NSJ]);                                                   \
+        d_ = rmin(rmax(d_, nlo), nhi);                                                                 \
+        const real delta = gp.shfl(d_, row);                                                            \
+        if (l == row) lam[NSJ] += delta;                                                                 \
+        UG_ROW_APPLY(delta, NACT)                                                        \
+      }                                                                                                  \
     }                                                                                                    \
     _Pragma("unroll") for (int so = 0; so < (NACT); so++) limv[so] = hi[NSJ + so] * gp.shfl(lam[NSJ], nidx[so]); \
     if (NT > 0) {                                                                                        \
       _Pragma("unroll") for (int so = 0; so < (NACT); so++) {                                            \
         const int a_ = max(NC, so * G), b_ = min(NC + NT, so * G + G);                                   \
-        _Pragma("unroll 1") for (int row = a_; row < b_; row++) {                                        \
-          UG_CONTACT_LOAD(row, so, false, NACT)                                                          \
-          const real bnd = limv[so];                                                                    \
-          real d_ = rfma(-w[NSJ + so], invd[NSJ + so], rhs[NSJ + so]);                                  \
-          d_ = rmin(rmax(d_, -bnd - lam[NSJ + so]), bnd - lam[NSJ + so]);                              \
-          if (!(bnd > 0._r)) d_ = 0._r;                                                                    \
-          const real delta = gp.shfl(d_, row - so * G);                                                 \
-          if (l == row - so * G) lam[NSJ + so] += delta;                                                 \
-          UG_CONTACT_APPLY(delta, 0._r, false, NACT)                                                      \
+        if (a_ < b_) {                                                                                   \
+          UG_TP_INIT(so, a_, NACT)                                                                       \
+          unsigned rb1 = UG_RB * (unsigned)(a_ + 1);                                                     \
+          _Pragma("unroll 1") for (int row = a_; row < b_; row++, rb1 += UG_RB) {                        \
+            UG_ROW_LOAD(so, row, rb1, NACT)                                                              \
+            const real bnd = limv[so];                                                                  \
+            real d_ = rfma(-w[NSJ + so], invd[NSJ + so], rhs[NSJ + so]);                                \
+            d_ = rmin(rmax(d_, -bnd - lam[NSJ + so]), bnd - lam[NSJ + so]);                            \
+            if (!(bnd > 0._r)) d_ = 0._r;                                                                  \
+            const real delta = gp.shfl(d_, row - so * G);                                               \
+            if (l == row - so * G) lam[NSJ + so] += delta;                                               \
+            UG_ROW_APPLY(delta, NACT)                                                    \
+          }                                                                                              \
         }                                                                                                \
       }                                                                                                  \
     }                                                                                                    \
     _Pragma("unroll") for (int so = 0; so < (NACT); so++) {                                              \
       const int a_ = max(fr0, so * G), b_ = min(Rc, so * G + G);                                         \
-      _Pragma("unroll 1") for (int row = a_; row < b_; row += 2) {                                       \
-        UG_CONTACT_LOAD(row, so, true, NACT)                                                             \
-        const int li = row - so * G;                                                                     \
-        real d_ = rfma(-w[NSJ + so], invd[NSJ + so], rhs[NSJ + so]);                                    \
-        const real sm = lam[NSJ + so] + d_;                                                             \
-        const real ot = __shfl_xor_sync(gp.mask, sm, 1, G); /* the pair's other tangent (pairs start on even rows) */ \
-        const real lm = limv[so];                           /* both lanes of a pair carry the same limit */ \
-        /* implicit cone, branch-free: inside the box |.| <= lm both tangents keep their value, else this one is */ \
-        /* scaled onto the circle of radius lm (rsqrt.approx.ftz: the argument is >= lm^2 > 0 whenever it is used) */ \
-        const real cs = rabs(lm * sm * rsqrt_ftz(rmax(rfma(sm, sm, ot * ot), 1e-30_r)));               \
-        const real cl = rmax(rabs(sm), rabs(ot)) > lm ? cs : lm;                                     \
-        const real sn = rmin(rmax(sm, -cl), cl);                                                      \
-        d_ = sn - lam[NSJ + so];                                                                         \
-        if ((l | 1) == (li | 1)) lam[NSJ + so] = sn;                                                     \
-        const real dA = gp.shfl(d_, li), dB = gp.shfl(d_, li + 1);                                      \
-        UG_CONTACT_APPLY(dA, dB, true, NACT)                                                             \
+      if (a_ < b_) {                                                                                     \
+        UG_TP_INIT(so, a_, NACT)                                                                         \
+        unsigned rb1 = UG_RB * (unsigned)(a_ + 1);                                                       \
+        _Pragma("unroll 1") for (int row = a_; row < b_; row += 2, rb1 += 2u * UG_RB) {                  \
+          UG_PAIR_LOAD(so, row, rb1, NACT)                                                               \
+          const int li = row - so * G;                                                                   \
+          real d_ = rfma(-w[NSJ + so], invd[NSJ + so], rhs[NSJ + so]);                                  \
+          const real sm = lam[NSJ + so] + d_;                                                           \
+          const real ot = __shfl_xor_sync(gp.mask, sm, 1, G); /* the pair's other tangent (pairs start on even rows) */ \
+          const real lm = limv[so];                           /* both lanes of a pair carry the same limit */ \
+          /* implicit cone, branch-free: inside the box |.| <= lm both tangents keep their value, else this one is */ \
+          /* scaled onto the circle of radius lm (rsqrt.approx.ftz: the argument is >= lm^2 > 0 whenever it is used) */ \
+          const real cs = rabs(lm * sm * rsqrt_ftz(rmax(rfma(sm, sm, ot * ot), 1e-30_r)));             \
+          const real cl = rmax(rabs(sm), rabs(ot)) > lm ? cs : lm;                                   \
+          const real sn = rmin(rmax(sm, -cl), cl);                                                    \
+          d_ = sn - lam[NSJ + so];                                                                       \
+          if ((l | 1) == (li | 1)) lam[NSJ + so] = sn;                                                   \
+          const real dA = gp.shfl(d_, li), dB = gp.shfl(d_, li + 1);                                    \
+          UG_PAIR_APPLY(dA, dB, NACT)                                                           \
+        }                                                                                                \
       }                                                                                                  \
     }                                                                                                    \
   }
@@ -618,9 +658,11 @@ __device__ __noinline__ real solve_and_integrate(S& s, const DevModel& M, const 
     if (!gp.any(res > UGP_RESIDUAL_THRESHOLD)) break;  // max over the rows <= threshold, as one vote
   }
 #undef UG_JOINT_STEP
-#undef UG_CONTACT_LOAD
-#undef UG_T_ADDR
-#undef UG_CONTACT_APPLY
+#undef UG_TP_INIT
+#undef UG_ROW_LOAD
+#undef UG_PAIR_LOAD
+#undef UG_ROW_APPLY
+#undef UG_PAIR_APPLY
 #undef UG_JOINT_SWEEP
 #undef UG_CONTACT_SWEEP
   *iters_out = it;
