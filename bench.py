@@ -35,10 +35,11 @@ WORKLOADS = {  # name -> (env, envs per GPU, BASELINE.json config index)
     'golf16384': ('Golf', 16384, None),
     'pushdiff16384': ('CubesPushDiff', 16384, None),
     'golfjoints16384': ('GolfJoints', 16384, None),
+    'box16384': ('Box', 16384, None),
 }
 # algorithmic HBM bytes per env-step (SURVEY.md §8d / DESIGN.md §5): state once in, once out, action in, obs/reward/flags out
 BYTES_PER_ENV_STEP = {'BallBalance': 562, 'TwoBallsBalance': 678, 'CubesPush': 606, 'CubesGrasp': 530, 'Golf': 606,
-                      'CubesPushDiff': 606, 'GolfJoints': 642}
+                      'CubesPushDiff': 606, 'GolfJoints': 642, 'Box': 586}
 METRIC = 'env-steps/sec (batched, device-timed)'
 
 
@@ -47,6 +48,10 @@ def action_sampler(env, n, gen, torch, device):
     if env == 'CubesGrasp':  # env_cubes_grasp_v0.py:74: [0,1]^2 x [-pi,pi]^6 x [0,1]
         a = torch.rand(n, 9, generator=gen, device=device)
         a[:, 2:8] = (a[:, 2:8] * 2 - 1) * 3.14159265
+        return a
+    if env == 'Box':         # env_box_v0.py:44: [-0.05, 0.05]^3 x [-pi/10, pi/10]^4 x [0, 0.085]
+        a = torch.rand(n, 8, generator=gen, device=device) * 2 - 1
+        a[:, :3] *= 0.05; a[:, 3:7] *= 0.314159265; a[:, 7] = (a[:, 7] + 1) * 0.0425
         return a
     return (torch.rand(n, 6 if env == 'GolfJoints' else 3, generator=gen, device=device) * 2 - 1) * 0.1
 
@@ -151,6 +156,8 @@ def cpu_arm(env, seconds, steps=None, warmup=0, envs_per_thread=4, seed=1234):
         def act():
             if env == 'CubesGrasp':
                 return np.concatenate([rng.uniform(0, 1, (envs_per_thread, 2)), rng.uniform(-np.pi, np.pi, (envs_per_thread, 6)), rng.uniform(0, 1, (envs_per_thread, 1))], 1)
+            if env == 'Box':
+                return np.concatenate([rng.uniform(-0.05, 0.05, (envs_per_thread, 3)), rng.uniform(-np.pi / 10, np.pi / 10, (envs_per_thread, 4)), rng.uniform(0, 0.085, (envs_per_thread, 1))], 1)
             return rng.uniform(-0.1, 0.1, (envs_per_thread, b.ad))
         for _ in range(warmup):
             b.step(act(), autoreset=True)

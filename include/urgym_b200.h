@@ -35,7 +35,9 @@ int urgym_real_bytes(void);
 /* 5 and 6 are the reference's variants of CubesPush / Golf: same world, other observation / action mapping
  * (urgym/envs/env_cubes_push_diff_v0.py:209-211; urgym/envs/env_golf_joints_v0.py:60-63,85,123-124,229-234). */
 enum { URGYM_BALL_BALANCE = 0, URGYM_TWO_BALLS_BALANCE = 1, URGYM_CUBES_PUSH = 2, URGYM_CUBES_GRASP = 3, URGYM_GOLF = 4,
-       URGYM_CUBES_PUSH_DIFF = 5, URGYM_GOLF_JOINTS = 6, URGYM_ENV_COUNT = 7 };
+       URGYM_CUBES_PUSH_DIFF = 5, URGYM_GOLF_JOINTS = 6,
+       URGYM_BOX = 7, /* urgym/envs/env_box_v0.py + urgym/urdf/skew-box-button.urdf: hinged door + button (cylinders as square prisms) */
+       URGYM_ENV_COUNT = 8 };
 enum { URGYM_OK = 0, URGYM_E_ARG = -1, URGYM_E_CUDA = -2, URGYM_E_STATE = -3 };
 enum { URGYM_STATE_FLOATS = 96, URGYM_MAX_CONTACTS = 32, URGYM_MAX_PAIRS = 160, URGYM_PAIR_WORDS = 5, URGYM_NUM_LINKS = 19, URGYM_NUM_DOF = 12 };
 

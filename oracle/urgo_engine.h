@@ -16,7 +16,7 @@
 
 namespace urgo {
 
-enum { ENV_BALL = 0, ENV_TWO = 1, ENV_PUSH = 2, ENV_GRASP = 3, ENV_GOLF = 4, ENV_PUSH_DIFF = 5, ENV_GOLF_JOINTS = 6, ENV_COUNT = 7 };
+enum { ENV_BALL = 0, ENV_TWO = 1, ENV_PUSH = 2, ENV_GRASP = 3, ENV_GOLF = 4, ENV_PUSH_DIFF = 5, ENV_GOLF_JOINTS = 6, ENV_BOX = 7, ENV_COUNT = 8 };
 // The two variants share their parent's world and differ in the action mapping / observation only:
 // env_cubes_push_diff_v0.py:209-211 (cube positions relative to the end effector), env_golf_joints_v0.py:60-63,85,123-124,229-234
 // (six joint displacements instead of an end-effector displacement; the six arm joints prepended to the observation).
@@ -42,9 +42,20 @@ struct ShapeDef {
   double mu, rest, roll, cbt;
 };
 
+// A body slot is a free rigid body (anchor 0) or, for the second articulated body of Box-v0 (skew-box-button.urdf: both of its
+// joints hang off the fixed base), a world-anchored 1-DoF body: a hinge (anchor 1: rotation about the world axis `axis` through
+// the body origin, which stays at `origin`) or a slider (anchor 2: translation along `axis` from `origin`, no rotation). Their
+// generalized inverse inertia is rank one: axis axis^T / inertia_axis (angular) or axis axis^T / mass (linear).
+struct Anchor {
+  int kind = 0; V3 axis, origin; double inertia_axis = 0, lower = 0, upper = 0;
+  V3 com;                 // hinge: merged centre of mass in the body frame (gravity torque about the axis)
+  double motor_force = 0; // slider: POSITION_CONTROL motor to coordinate 0 with this force limit (env_box_v0.py:176), 0 = none
+};
 struct Scene {
   int env_type = 0, nfree = 0;
   double gravity = -9.8;
+  V3 base;                // robot base position (env_box_v0.py:55: (0, 0.5, 0); every other env: the origin)
+  Anchor anchor[MAXFREE];
   double fmass[MAXFREE]; V3 finertia[MAXFREE];
   std::vector<ShapeDef> shapes;
   std::vector<std::pair<int, int>> pairs;
@@ -139,6 +150,33 @@ inline Scene make_scene(int env_type_full) {
       sc.shapes.push_back(ground);
       break;
     }
+    case ENV_BOX: {  // env_box_v0.py:55-85, urgym/urdf/skew-box-button.urdf (URDF_MERGE_FIXED_LINKS | URDF_USE_SELF_COLLISION, fixed base)
+      sc.nfree = 2; sc.obs_dim = 7; sc.act_dim = 8; sc.max_steps = 200; sc.gravity = -10.0;
+      sc.base = V3(0, 0.5, 0);
+      // body 1: the door (link `door` + the welded handle bars h1, h2, h3), hinge about y at (0.075, 0, 0.1), limits [0, 2];
+      // inertia about the axis: iyy = 0.5 of the door link (no inertial origin: its COM is the hinge) + the bars as point masses
+      const double mh1 = 0.05, mh3 = 0.1;
+      sc.anchor[0].kind = 1; sc.anchor[0].axis = V3(0, 1, 0); sc.anchor[0].origin = V3(0.075, 0, 0.1); sc.anchor[0].lower = 0; sc.anchor[0].upper = 2;
+      sc.anchor[0].inertia_axis = 0.5 + 2 * mh1 * (0.13 * 0.13 + 0.025 * 0.025) + mh3 * (0.13 * 0.13 + 0.05 * 0.05);
+      sc.fmass[0] = 0.1 + 2 * mh1 + mh3; sc.finertia[0] = V3(1, 1, 1);
+      sc.anchor[0].com = V3(-0.13 * (2 * mh1 + mh3), 0, 2 * mh1 * 0.025 + mh3 * 0.05) * (1.0 / sc.fmass[0]);
+      // body 2: the button, slider along z from (0, 0, 0.07), limits [-0.05, 0], position motor with force 1 (reset_box)
+      sc.anchor[1].kind = 2; sc.anchor[1].axis = V3(0, 0, 1); sc.anchor[1].origin = V3(0, 0, 0.07); sc.anchor[1].lower = -0.05; sc.anchor[1].upper = 0;
+      sc.anchor[1].motor_force = 1.0; sc.fmass[1] = 0.01; sc.finertia[1] = V3(1, 1, 1);
+      // collision shapes. The URDF's four cylinders (handle posts r = 5 mm, bar r = 10 mm, button r = 20 mm) enter as their
+      // circumscribed square prisms: the narrowphase has boxes, spheres and the gripper's polytopes
+      sc.shapes.push_back(mk_box(1, 0, V3(-0.076, 0, 0), V3(0.08, 0.1, 0.005), bm));          // door plate
+      sc.shapes.push_back(mk_box(1, 1, V3(-0.13, 0.05, 0.025), V3(0.005, 0.005, 0.025), bm));  // h1
+      sc.shapes.push_back(mk_box(1, 2, V3(-0.13, -0.05, 0.025), V3(0.005, 0.005, 0.025), bm)); // h2
+      sc.shapes.push_back(mk_box(1, 3, V3(-0.13, 0, 0.05), V3(0.01, 0.05, 0.01), 1.0));        // h3 (contact_coefficients mu = 1), axis along y
+      sc.shapes.push_back(mk_box(2, 0, V3(), V3(0.02, 0.02, 0.025), bm));                      // button
+      sc.shapes.push_back(mk_box(-1, 0, V3(0.075, 0, 0.045), V3(0.005, 0.1, 0.045), bm));      // box1..box4: the walls
+      sc.shapes.push_back(mk_box(-1, 1, V3(-0.075, 0, 0.045), V3(0.005, 0.1, 0.045), bm));
+      sc.shapes.push_back(mk_box(-1, 2, V3(0, 0.1, 0.045), V3(0.075, 0.005, 0.045), bm));
+      sc.shapes.push_back(mk_box(-1, 3, V3(0, -0.1, 0.045), V3(0.075, 0.005, 0.045), bm));
+      sc.shapes.push_back(mk_box(-1, 4, V3(0, 0, -5.0), V3(15, 15, 5), bp().plane_mu));        // plane.urdf at the origin
+      break;
+    }
   }
   if (env_type_full == ENV_GOLF_JOINTS) { sc.obs_dim = 15; sc.act_dim = 6; }
   int ns = (int)sc.shapes.size();
@@ -147,9 +185,14 @@ inline Scene make_scene(int env_type_full) {
   auto is_robot = [&](int i) { return sc.shapes[i].body == 0; };
   for (int a = 0; a < ns; a++) for (int b = a + 1; b < ns; b++)
     if (is_free(a) && is_free(b) && sc.shapes[a].body != sc.shapes[b].body) sc.pairs.push_back({a, b});
-  for (int a = 0; a < ns; a++) for (int b = 0; b < ns; b++) if (is_free(a) && is_static(b)) sc.pairs.push_back({a, b});
-  for (int a = 0; a < ns; a++) for (int b = 0; b < ns; b++) if (is_robot(a) && is_free(b)) sc.pairs.push_back({a, b});
-  for (int a = 0; a < ns; a++) for (int b = 0; b < ns; b++) if (is_robot(a) && is_static(b)) sc.pairs.push_back({a, b});
+  // (Box-v0: door and button are anchored inside the box and never reach the ground plane)
+  for (int a = 0; a < ns; a++) for (int b = 0; b < ns; b++)
+    if (is_free(a) && is_static(b) && !(env_type == ENV_BOX && sc.shapes[b].link == 4)) sc.pairs.push_back({a, b});
+  // Box-v0: the upper arm links (the last four of LINK_ORDER: 4, 3, 2, 1) are tested against the ground plane only, which keeps
+  // the pair list within the kernel's 160 (they cannot reach the box without the wrist or the gripper touching it first)
+  auto arm_only = [&](int a, int b) { return env_type == ENV_BOX && a >= 13 && !(is_static(b) && sc.shapes[b].link == 4); };
+  for (int a = 0; a < ns; a++) for (int b = 0; b < ns; b++) if (is_robot(a) && is_free(b) && !arm_only(a, b)) sc.pairs.push_back({a, b});
+  for (int a = 0; a < ns; a++) for (int b = 0; b < ns; b++) if (is_robot(a) && is_static(b) && !arm_only(a, b)) sc.pairs.push_back({a, b});
   return sc;
 }
 
@@ -198,6 +241,7 @@ struct Robot {
   M6 IA[URG_NLINK]; double D[URG_NLINK], u[URG_NLINK];
   int dof_of_link[URG_NLINK]; uint32_t anc[URG_NLINK];  // anc: bitmask over dofs of joints on the path to the base
   Q4 jquat[URG_NLINK];
+  V3 base;  // position of the base link in the world (robot.py:39-41: base_pos)
 
   Robot() {
     std::memset(q, 0, sizeof(q)); std::memset(qd, 0, sizeof(qd));
@@ -216,7 +260,7 @@ struct Robot {
   void fk() {
     for (int i = 0; i < URG_NLINK; i++) {
       const UrgLinkModel& L = URG_LINKS[i];
-      V3 pp; Q4 pq; M3 pR = M3::identity();
+      V3 pp = base; Q4 pq; M3 pR = M3::identity();
       if (L.parent >= 0) { pp = p[L.parent]; pq = quat[L.parent]; pR = R[L.parent]; }
       p[i] = pp + pR * V3(L.jxyz[0], L.jxyz[1], L.jxyz[2]);
       Q4 qi = pq * jquat[i];
@@ -314,7 +358,15 @@ struct World {
   long st_ticks = 0, st_iters = 0, st_rows = 0, st_contacts = 0, st_rowiters = 0;  // profiling counters (tests / design notes)
   long st_hist_rows[192] = {0}, st_hist_nc[64] = {0}, st_hist_nnc[32] = {0}, st_hist_roll[16] = {0};
 
-  explicit World(int env_type) : sc(make_scene(env_type)) { for (int i = 0; i < NMOTOR; i++) target[i] = 0; }
+  explicit World(int env_type) : sc(make_scene(env_type)) { for (int i = 0; i < NMOTOR; i++) target[i] = 0; rob.base = sc.base; }
+
+  // coordinate and velocity of an anchored body's single degree of freedom
+  double anchor_q(int b) const {
+    const Anchor& A = sc.anchor[b];
+    if (A.kind == 1) { const Q4& q = fb[b].quat; return 2.0 * std::atan2(q.x * A.axis.x + q.y * A.axis.y + q.z * A.axis.z, q.w); }
+    return dot(fb[b].pos - A.origin, A.axis);
+  }
+  double anchor_qd(int b) const { return sc.anchor[b].kind == 1 ? dot(fb[b].ang, sc.anchor[b].axis) : dot(fb[b].lin, sc.anchor[b].axis); }
 
   BoxW world_box(const ShapeDef& s) const {
     BoxW b;
@@ -390,14 +442,17 @@ struct World {
       M3 Iinv = rot_diag(R, inv_i);
       if (lin) { r.Jl[k] = dir * sgn; r.Ja[k] = cross(P - fb[b].pos, dir) * sgn; }
       else { r.Jl[k] = V3(); r.Ja[k] = dir * sgn; }
-      r.Dl[k] = r.Jl[k] * (1.0 / sc.fmass[b]); r.Da[k] = Iinv * r.Ja[k];
+      const Anchor& An = sc.anchor[b];
+      if (An.kind == 0) { r.Dl[k] = r.Jl[k] * (1.0 / sc.fmass[b]); r.Da[k] = Iinv * r.Ja[k]; }
+      else if (An.kind == 1) { r.Dl[k] = V3(); r.Da[k] = An.axis * (dot(An.axis, r.Ja[k]) / An.inertia_axis); }
+      else { r.Dl[k] = An.axis * (dot(An.axis, r.Jl[k]) / sc.fmass[b]); r.Da[k] = V3(); }
     }
   }
   void finish_row(Row& r) {
     double den = 0;
     if (r.has_robot) { rob.minv_mul(r.Jr, r.Dr); for (int d = 0; d < NDOF; d++) den += r.Jr[d] * r.Dr[d]; }
     for (int k = 0; k < 2; k++) if (r.f[k] >= 0) den += dot(r.Jl[k], r.Dl[k]) + dot(r.Ja[k], r.Da[k]);
-    r.invd = 1.0 / den;
+    r.invd = den > 1e-20 ? 1.0 / den : 0.0;  // a row no body can move along (anchored bodies: a tangent across the hinge axis) stays inert
   }
   double row_vel(const Row& r, const double* qd) const {
     double s = 0;
@@ -425,7 +480,7 @@ struct World {
     else if (sum > r.hi) { delta = r.hi - r.applied; r.applied = r.hi; }
     else r.applied = sum;
     row_apply(r, dv, delta);
-    return delta / r.invd;
+    return r.invd > 0 ? delta / r.invd : 0.0;
   }
 
   // One 1/240 s tick of stepSimulation.
@@ -441,6 +496,21 @@ struct World {
       if (!fb[b].active) continue;
       FreeBody& B = fb[b];
       M3 R = quat_to_mat(B.quat);
+      if (sc.anchor[b].kind == 1) {        // hinge: gravity torque of the merged COM about the axis, Bullet's angular damping
+        const Anchor& An = sc.anchor[b];
+        double w = dot(B.ang, An.axis);
+        double tq = dot(An.axis, cross(R * An.com, V3(0, 0, sc.fmass[b] * sc.gravity)));
+        w += dt * (tq / An.inertia_axis - w * (bp().ang_damping + bp().ang_damping * std::fabs(w)));
+        B.ang = An.axis * w; B.lin = V3();
+        continue;
+      }
+      if (sc.anchor[b].kind == 2) {        // slider: gravity and linear damping along the axis
+        const Anchor& An = sc.anchor[b];
+        double v = dot(B.lin, An.axis);
+        v += dt * (An.axis.z * sc.gravity - v * (bp().lin_damping + bp().lin_damping * std::fabs(v)));
+        B.lin = An.axis * v; B.ang = V3();
+        continue;
+      }
       V3 acc = V3(0, 0, sc.gravity) - B.lin * (bp().lin_damping + bp().lin_damping * norm(B.lin));
       V3 wl = tmul(R, B.ang);
       V3 I = sc.finertia[b];
@@ -484,6 +554,33 @@ struct World {
       r.rhs = (-pos_err * bp().erp / dt - rel) * r.invd; r.lo = -BP_GEAR_MAX_FORCE * dt; r.hi = BP_GEAR_MAX_FORCE * dt;
       nc.push_back(r);
     }
+    // joint rows of the anchored bodies (Box-v0: btMultiBodyJointLimitConstraint of door and button when violated, the
+    // button's position motor): solved after the robot's joint rows and before the contact normals, in this order
+    std::vector<Row> nb;
+    for (int b = 0; b < sc.nfree; b++) {
+      const Anchor& An = sc.anchor[b];
+      if (An.kind == 0 || !fb[b].active) continue;
+      const double qa = anchor_q(b), va = anchor_qd(b);
+      for (int side = 0; side < 2; side++) {
+        double pen = side == 0 ? qa - An.lower : An.upper - qa;
+        if (pen > 0) continue;
+        Row r; r.f[0] = b; double sg = side == 0 ? 1.0 : -1.0;
+        r.Jl[0] = An.kind == 2 ? An.axis * sg : V3(); r.Ja[0] = An.kind == 1 ? An.axis * sg : V3();
+        r.Dl[0] = An.kind == 2 ? r.Jl[0] * (1.0 / sc.fmass[b]) : V3(); r.Da[0] = An.kind == 1 ? r.Ja[0] * (1.0 / An.inertia_axis) : V3();
+        finish_row(r);
+        r.rhs = (-pen * bp().erp / dt - sg * va) * r.invd; r.lo = 0; r.hi = BP_LIMIT_MAX_IMPULSE;
+        nb.push_back(r);
+      }
+      if (An.motor_force > 0) {
+        Row r; r.f[0] = b;
+        r.Jl[0] = An.kind == 2 ? An.axis : V3(); r.Ja[0] = An.kind == 1 ? An.axis : V3();
+        r.Dl[0] = An.kind == 2 ? r.Jl[0] * (1.0 / sc.fmass[b]) : V3(); r.Da[0] = An.kind == 1 ? r.Ja[0] * (1.0 / An.inertia_axis) : V3();
+        finish_row(r);
+        double want = bp().motor_kp * (0.0 - qa) / dt + (1.0 - bp().motor_kd) * va;
+        r.rhs = (want - va) * r.invd; r.lo = -An.motor_force * dt; r.hi = An.motor_force * dt;
+        nb.push_back(r);
+      }
+    }
     for (size_t ci = 0; ci < contacts.size(); ci++) {  // contacts (rows P5, P6)
       const Contact& c = contacts[ci];
       const ShapeDef& A = sc.shapes[c.sa]; const ShapeDef& B = sc.shapes[c.sb];
@@ -517,6 +614,7 @@ struct World {
       double res = 0;
       int nn = (int)nc.size();
       for (int j = 0; j < nn; j++) { int idx = (it & 1) ? j : nn - 1 - j; double r = resolve(nc[idx], dv); res = std::fmax(res, r * r); }
+      for (auto& r : nb) { double x = resolve(r, dv); res = std::fmax(res, x * x); }
       for (auto& r : nr) { double x = resolve(r, dv); res = std::fmax(res, x * x); }
       for (auto& t : tr) {
         double tot = nr[t.nidx].applied;
@@ -540,13 +638,13 @@ struct World {
           if (sb < -cb) { db = -cb - b.applied; b.applied = -cb; } else if (sb > cb) { db = cb - b.applied; b.applied = cb; } else b.applied = sb;
         } else { a.applied = sa; b.applied = sb; }
         row_apply(a, dv, da); row_apply(b, dv, db);
-        double ra = da / a.invd, rb = db / b.invd;
+        double ra = a.invd > 0 ? da / a.invd : 0.0, rb = b.invd > 0 ? db / b.invd : 0.0;
         res = std::fmax(res, std::fmax(ra * ra, rb * rb));
       }
       if (res <= BP_RESIDUAL_THRESHOLD) { it++; break; }
     }
     last_iters = it;
-    { long R = (long)(nc.size() + nr.size() + tr.size() + fr.size()); st_ticks++; st_iters += it; st_rows += R; st_contacts += (long)contacts.size(); st_rowiters += R * it; st_hist_rows[R < 191 ? R : 191]++; st_hist_nc[contacts.size() < 63 ? contacts.size() : 63]++; st_hist_roll[tr.size() / 2 < 15 ? tr.size() / 2 : 15]++; st_hist_nnc[nc.size() < 31 ? nc.size() : 31]++; }
+    { long R = (long)(nc.size() + nb.size() + nr.size() + tr.size() + fr.size()); st_ticks++; st_iters += it; st_rows += R; st_contacts += (long)contacts.size(); st_rowiters += R * it; st_hist_rows[R < 191 ? R : 191]++; st_hist_nc[contacts.size() < 63 ? contacts.size() : 63]++; st_hist_roll[tr.size() / 2 < 15 ? tr.size() / 2 : 15]++; st_hist_nnc[nc.size() < 31 ? nc.size() : 31]++; }
     // --- apply and integrate (semi-implicit Euler; exponential map for free-body orientation)
     for (int d = 0; d < NDOF; d++) {
       rob.qd[d] = std::fmax(-BP_MAX_COORD_VEL, std::fmin(BP_MAX_COORD_VEL, rob.qd[d] + dv.r[d]));
@@ -557,6 +655,7 @@ struct World {
       FreeBody& B = fb[b];
       B.lin += dv.l[b]; B.ang += dv.a[b];
       B.pos += B.lin * dt;
+      if (sc.anchor[b].kind == 2) continue;
       double wn = norm(B.ang);
       if (wn * dt > BP_ANGULAR_MOTION_THRESHOLD) wn = BP_ANGULAR_MOTION_THRESHOLD / dt;
       V3 ax;

@@ -6,6 +6,7 @@
 //   CubesPush        /root/reference/urgym/envs/env_cubes_push_v0.py:104-246
 //   CubesGrasp       /root/reference/urgym/envs/env_cubes_grasp_v0.py:100-327
 //   Golf             /root/reference/urgym/envs/env_golf_v0.py:104-358
+//   Box              /root/reference/urgym/envs/env_box_v0.py:110-190 (fixed 120 ticks per step instead of wait_until_stable)
 // and the robot helper /root/reference/urgym/base/robot.py:85-128,213-218. Episode limits from
 // /root/reference/urgym/envs/__init__.py:10-44 (the TimeLimit wrapper's `truncated`).
 //
@@ -159,6 +160,12 @@ struct Env {
         ticks += settle();
         break;
       }
+      case ENV_BOX: {  // env_box_v0.py:178-185: move_ee to the current pose, reset_box(): both joints to 0, button motor on
+        ee_pose(ep, eq);
+        move_ee_end(ep, eq);
+        for (int b = 0; b < 2; b++) spawn(b, w.sc.anchor[b].origin, Q4());
+        break;
+      }
       case ENV_GOLF: {
         vertical = Q4(0.0, 0.0, -0.70, 0.70);
         move_ee_end(V3(0.0, -0.60, 0.40), vertical);
@@ -200,6 +207,10 @@ struct Env {
         o[10] = w.fb[0].pos.x; o[11] = w.fb[0].pos.y; o[12] = w.fb[0].pos.z;
         o[13] = w.fb[0].quat.x; o[14] = w.fb[0].quat.y; o[15] = w.fb[0].quat.z; o[16] = w.fb[0].quat.w;
         break;
+      case ENV_BOX:  // env_box_v0.py:161-170: robot.get_joint_obs()['ee_pos'] = ee position + quaternion
+        ee_pose(ep, eq);
+        o[0] = ep.x; o[1] = ep.y; o[2] = ep.z; o[3] = eq.x; o[4] = eq.y; o[5] = eq.z; o[6] = eq.w;
+        break;
       case ENV_GOLF: {
         V3 s = club_foot(), b = w.fb[1].pos, h(0, -0.6, 0.02);
         if (variant == ENV_GOLF_JOINTS) { for (int i = 0; i < 6; i++) o[i] = w.rob.q[i]; o += 6; }  // env_golf_joints_v0.py:229-234
@@ -232,6 +243,12 @@ struct Env {
         ee_pose(ep, eq);
         move_ee_end(ep + V3(a[0], a[1], a[2]), vertical);
         break;
+      case ENV_BOX: {  // env_box_v0.py:124-126: new_pose = ee_pose (position + quaternion, 7 numbers) + action[:-1], component-wise
+        ee_pose(ep, eq);
+        move_ee_end(ep + V3(a[0], a[1], a[2]), Q4(eq.x + a[3], eq.y + a[4], eq.z + a[5], eq.w + a[6]));
+        move_gripper(a[7]);
+        break;
+      }
       case ENV_GRASP: {
         double a0 = a[0], a1 = a[1];
         int sel = (a0 + a1 == 0) ? (u < 0.5 ? 0 : 1) : (u * (a0 + a1) < a0 ? 0 : 1);
@@ -289,6 +306,14 @@ struct Env {
         rew -= 0.1;
         break;
       }
+      case ENV_BOX: {  // env_box_v0.py:141-159 (button_touch_mode='any', the registered default), :129-137
+        const double door = w.anchor_q(0), button = w.anchor_q(1);
+        if (!approached) { if (door > 1.9) { approached = true; rew = 1; } }          // box_opened
+        else if (!grasped) { if (button < -0.02) { grasped = true; rew = 1; } }       // button_pressed
+        else if (door < 0.1) { rew = 1; term = true; succ = true; }                   // box_closed
+        rew -= 0.1;
+        break;
+      }
       case ENV_GOLF: {
         V3 hole(0, -0.6, 0.02), ball = w.fb[1].pos;
         bool in_fingers = touch([](const ShapeDef& A, const ShapeDef& B, void*) { return A.body == 0 && B.body == 1 && A.link >= 9 && A.link <= 18; });
@@ -316,7 +341,9 @@ struct Env {
   // One gym step without auto-reset. Returns settle ticks.
   int step(const double* a, double u, double* obs, double* reward, uint8_t* terminated, uint8_t* truncated, uint8_t* success) {
     double rew = prologue(a, u);
-    int n = settle();
+    int n;
+    if (env_type == ENV_BOX) { for (n = 0; n < 120; n++) w.tick(); total_ticks += n; ev(EV_TICKS, {(double)n}); }  // env_box_v0.py:127-128
+    else n = settle();
     epilogue(rew, obs, reward, terminated, truncated, success);
     return n;
   }
@@ -538,6 +565,11 @@ void urgo_fk(const double* q, double* out) {
 }
 void urgo_ik(const double* q, const double* target7, double* out6) {
   World w(ENV_BALL); std::memcpy(w.rob.q, q, sizeof(double) * NDOF);
+  w.ik(V3(target7[0], target7[1], target7[2]), Q4(target7[3], target7[4], target7[5], target7[6]), out6);
+}
+// the same with the robot's base link at `base3` (Box-v0: (0, 0.5, 0), env_box_v0.py:55)
+void urgo_ik_base(const double* q, const double* target7, const double* base3, double* out6) {
+  World w(ENV_BALL); std::memcpy(w.rob.q, q, sizeof(double) * NDOF); w.rob.base = V3(base3[0], base3[1], base3[2]);
   w.ik(V3(target7[0], target7[1], target7[2]), Q4(target7[3], target7[4], target7[5], target7[6]), out6);
 }
 void urgo_gripper_center(const double* q, double* out3) {

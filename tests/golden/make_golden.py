@@ -89,6 +89,7 @@ class ScriptedBullet(types.ModuleType):
     POSITION_CONTROL, VELOCITY_CONTROL, TORQUE_CONTROL = 2, 0, 1
     GEOM_SPHERE, GEOM_BOX, GEOM_CYLINDER, GEOM_MESH = 2, 3, 4, 5
     COV_ENABLE_GUI, URDF_ENABLE_CACHED_GRAPHICS_SHAPES = 1, 1024
+    URDF_USE_SELF_COLLISION, URDF_MERGE_FIXED_LINKS = 8, 512   # pybullet's values (env_box_v0.py:85)
 
     def __init__(self, robot_joints):
         super().__init__('pybullet')
@@ -154,7 +155,8 @@ class ScriptedBullet(types.ModuleType):
     def changeDynamics(self, *a, **k): self._rec('changeDynamics', *a, **k)
     def createConstraint(self, *a, **k): self._rec('createConstraint', *a, **k); return len(self.log)
     def changeConstraint(self, *a, **k): self._rec('changeConstraint', *a[1:], **k)
-    def resetJointState(self, body, joint, value, *a, **k):
+    def resetJointState(self, body, joint, value=None, *a, targetValue=None, **k):
+        value = targetValue if value is None else value   # env_box_v0.py:173-174 passes it by keyword
         self._rec('resetJointState', joint, value); self.joint_pos[(body, joint)] = float(value)
 
     def setJointMotorControl2(self, body, joint, mode, *a, **k):

@@ -6,7 +6,7 @@ import subprocess
 import numpy as np
 
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
-ENV_TYPES = {'BallBalance': 0, 'TwoBallsBalance': 1, 'CubesPush': 2, 'CubesGrasp': 3, 'Golf': 4, 'CubesPushDiff': 5, 'GolfJoints': 6}
+ENV_TYPES = {'BallBalance': 0, 'TwoBallsBalance': 1, 'CubesPush': 2, 'CubesGrasp': 3, 'Golf': 4, 'CubesPushDiff': 5, 'GolfJoints': 6, 'Box': 7}
 MAXC = 64          # width of the oracle's contact-pair export (urgo_export_maxc); the oracle itself keeps every point
 STATE_SLOTS = 96
 _lib = None
@@ -172,8 +172,13 @@ def fk(q):
     out = np.zeros((19, 7)); q = _d(q); lib().urgo_fk(_p(q), _p(out)); return out
 
 
-def ik(q, target7):
-    out = np.zeros(6); q = _d(q); t = _d(target7); lib().urgo_ik(_p(q), _p(t), _p(out)); return out
+def ik(q, target7, base=None):
+    out = np.zeros(6); q = _d(q); t = _d(target7)
+    if base is None:
+        lib().urgo_ik(_p(q), _p(t), _p(out))
+    else:
+        b = _d(np.asarray(base, dtype=np.float64)); lib().urgo_ik_base(_p(q), _p(t), _p(b), _p(out))
+    return out
 
 
 def gripper_center(q):

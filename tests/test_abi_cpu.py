@@ -50,14 +50,14 @@ def test_no_torch_or_cxx_types_in_the_signatures():
 
 
 def test_static_queries_work_without_a_device(L):
-    dims = {0: (6, 3, 500), 1: (9, 3, 500), 2: (9, 3, 50), 3: (17, 9, 20), 4: (9, 3, 100), 5: (9, 3, 50), 6: (15, 6, 100)}
+    dims = {0: (6, 3, 500), 1: (9, 3, 500), 2: (9, 3, 50), 3: (17, 9, 20), 4: (9, 3, 100), 5: (9, 3, 50), 6: (15, 6, 100), 7: (7, 8, 200)}
     for t, (od, ad, ms) in dims.items():
         assert (L.urgym_obs_dim(t), L.urgym_act_dim(t), L.urgym_max_episode_steps(t)) == (od, ad, ms)
         g, sm = C.c_int(), C.c_int()
         assert L.urgym_kernel_info(t, C.byref(g), C.byref(sm)) == 0
-        assert g.value == 32 and 0 < sm.value <= (17, 17, 21, 17, 36, 21, 36)[t] * 1024   # 13 (10 CubesPush, 6 Golf scenes) resident envs per SM
-    assert L.urgym_obs_dim(7) < 0
-    assert L.urgym_real_bytes() == 4 and [L.urgym_num_pairs(t) for t in range(7)] == [73, 94, 73, 35, 134, 73, 134]
+        assert g.value == 32 and 0 < sm.value <= (17, 17, 21, 17, 36, 21, 36, 21)[t] * 1024   # 13 (10 CubesPush / Box, 6 Golf scenes) resident envs per SM
+    assert L.urgym_obs_dim(8) < 0
+    assert L.urgym_real_bytes() == 4 and [L.urgym_num_pairs(t) for t in range(8)] == [73, 94, 73, 35, 134, 73, 134, 158]
 
 
 def test_shape_tables_agree_with_the_oracle(L):

@@ -43,7 +43,9 @@ def test_no_cpu_fallback_for_the_env_classes():
     with pytest.raises(UrgymError):
         E.URGymVectorEnv('URGym/Golf-v0', 8)
     with pytest.raises(ValueError):
-        E.URGymVectorEnv('URGym/Box-v0', 8)
+        E.URGymVectorEnv('URGym/Nope-v0', 8)
+    with pytest.raises(NotImplementedError):
+        E.make('URGym/Box-v0', button_touch_mode='fingers')   # only the registered default 'any' is backed
     from urgym_b200.sb3_vec_env import URGymSB3VecEnv
     with pytest.raises(UrgymError):
         URGymSB3VecEnv('URGym/CubesPush-v0', 8)

@@ -32,7 +32,8 @@ def test_registry_ids_and_episode_limits():
     for env_id, spec in E.SPECS.items():
         assert env_id in reg
         assert reg[env_id]['max_episode_steps'] == spec[1]
-        assert reg[env_id]['entry_point'].endswith(':' + SCENE_OF.get(spec[0], spec[0]))   # the variants reuse the class names
+        cls = {'Box': 'BoxManipulation'}.get(spec[0], SCENE_OF.get(spec[0], spec[0]))                # the variants reuse the class names
+        assert reg[env_id]['entry_point'].endswith(':' + cls)
         assert O.OracleBatch(spec[0], 1).max_steps == spec[1]
     assert sorted(set(reg) - set(E.SPECS)) == sorted(E.UNSUPPORTED)
 

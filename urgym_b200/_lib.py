@@ -11,7 +11,7 @@ SO_PATH = os.environ.get('URGYM_SO') or os.path.join(HERE, 'liburgym_b200.so')  
 # the parity build: same sources and entry points with urgym_real = double (include/urgym_b200.h, urgym_b200/build.py)
 SO_PATH_F64 = os.environ.get('URGYM_SO_F64') or os.path.join(HERE, 'liburgym_b200_f64.so')
 
-ENV_TYPES = {'BallBalance': 0, 'TwoBallsBalance': 1, 'CubesPush': 2, 'CubesGrasp': 3, 'Golf': 4, 'CubesPushDiff': 5, 'GolfJoints': 6}
+ENV_TYPES = {'BallBalance': 0, 'TwoBallsBalance': 1, 'CubesPush': 2, 'CubesGrasp': 3, 'Golf': 4, 'CubesPushDiff': 5, 'GolfJoints': 6, 'Box': 7}
 STATE_FLOATS = 96
 MAX_CONTACTS = 32      # width of the manifold-point export (include/urgym_b200.h: URGYM_MAX_CONTACTS)
 PAIR_WORDS = 5         # uint32 words of the per-pair contact mask (URGYM_PAIR_WORDS)

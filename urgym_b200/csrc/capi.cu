@@ -74,7 +74,7 @@ int group_size() { return 32; }
 // reset ticks of the slowest env) and the fused launch, which starts every reset the moment its env finishes, is 0-3 % ahead;
 // from 8192 envs on the launch is throughput-bound and the split form wins by 6-20 %.
 bool default_split_reset(int env_type, int num_envs) {
-  static const bool dflt[UG_ENV_COUNT] = {true, true, false, false, false, false, false};
+  static const bool dflt[UG_ENV_COUNT] = {true, true, false, false, false, false, false, false};
   const char* e = getenv("URGYM_SPLIT_RESET");
   return e ? atoi(e) != 0 : (dflt[env_type] && num_envs > 4096);
 }
@@ -124,7 +124,8 @@ int launch(urgym_handle h, KParams& P, void* stream) {
     case 3: return launch_env<3>(h, P, st);
     case 4: return launch_env<4>(h, P, st);
     case 5: return launch_env<5>(h, P, st);
-    default: return launch_env<6>(h, P, st);
+    case 6: return launch_env<6>(h, P, st);
+    default: return launch_env<7>(h, P, st);
   }
 }
 
@@ -169,7 +170,8 @@ int launch_static_any(int env_type, int N, int device, const KParams& P, cudaStr
     case 3: return launch_static<3>(N, device, P, st);
     case 4: return launch_static<4>(N, device, P, st);
     case 5: return launch_static<5>(N, device, P, st);
-    default: return launch_static<6>(N, device, P, st);
+    case 6: return launch_static<6>(N, device, P, st);
+    default: return launch_static<7>(N, device, P, st);
   }
 }
 
@@ -434,7 +436,7 @@ int urgym_kernel_info(int env_type, int* group_lanes, int* smem_bytes_per_env) {
   if (env_type < 0 || env_type >= UG_ENV_COUNT || !group_lanes || !smem_bytes_per_env) return fail(URGYM_E_ARG, "urgym_kernel_info: bad arguments");
   *group_lanes = group_size();
   const int sz[UG_ENV_COUNT] = {(int)sizeof(EnvSmem<0>), (int)sizeof(EnvSmem<1>), (int)sizeof(EnvSmem<2>), (int)sizeof(EnvSmem<3>), (int)sizeof(EnvSmem<4>),
-                                (int)sizeof(EnvSmem<5>), (int)sizeof(EnvSmem<6>)};
+                                (int)sizeof(EnvSmem<5>), (int)sizeof(EnvSmem<6>), (int)sizeof(EnvSmem<7>)};
   *smem_bytes_per_env = sz[env_type];
   return URGYM_OK;
 }

@@ -31,7 +31,7 @@ struct SmemT {
   // ---- state that lives across the ticks of one gym step
   real q[UG_NDOF], qd[UG_NDOF], tgt[8];
   real fpos[UG_MAXFREE][3], fquat[UG_MAXFREE][4], flin[UG_MAXFREE][3], fang[UG_MAXFREE][3];
-  int flags, ncon, ovf, pad1;   // ovf: ticks of this launch whose manifold points / rolling manifolds exceeded the capacity
+  int flags, ncon, ovf, npseudo;   // npseudo: pseudo contacts at the head of con (anchored bodies' joint rows); ovf: ticks of this launch whose manifold points / rolling manifolds exceeded the capacity
   unsigned hit[UG_HITWORDS];     // pairs of the scene's pair list with at least one manifold point this tick (set before the cap)
   // ---- per tick
   real vstar[32];
@@ -65,6 +65,26 @@ struct SmemT {
 #define FL_APPROACHED 4
 #define FL_GRASPED 8
 #define FL_BODY0 16
+
+// Pseudo contacts: joint rows of the anchored bodies (Box-v0 door / button limits, button motor) travel as manifold entries at
+// the head of s.con so that they are solved between the robot's joint rows and the contact normals, as the checker does.
+// Con::shapes of such an entry: UG_PSEUDO | kind (1 limit, 2 motor) | 4 when the row is angular (hinge).
+#define UG_PSEUDO 0x10000
+// linear part of an anchored or free body's generalized inverse inertia applied to a force direction
+UG_DEV f3 lin_inv(const DevModel& M, int b, f3 J) {
+  const int a = M.fanchor[b];
+  if (a == 0) return J * (1.0_r / M.fmass[b]);
+  if (a == 1) return mk3(0, 0, 0);
+  const f3 ax = ld3(M.faxis[b]);
+  return ax * (dot(ax, J) / M.fmass[b]);
+}
+// coordinate of an anchored body's single degree of freedom (angle about / offset along faxis)
+template <class S>
+UG_DEV real anchor_q(const S& s, const DevModel& M, int b) {
+  const f3 ax = ld3(M.faxis[b]);
+  if (M.fanchor[b] == 1) return 2.0_r * ratan2(s.fquat[b][0] * ax.x + s.fquat[b][1] * ax.y + s.fquat[b][2] * ax.z, s.fquat[b][3]);
+  return dot(ld3(s.fpos[b]) - ld3(M.forigin[b]), ax);
+}
 
 enum { RT_LIM_LO = 0, RT_LIM_HI = 1, RT_MOTOR = 2, RT_GEAR = 3, RT_NORMAL = 4, RT_ROLL = 5, RT_FRIC = 6, RT_PAD = 7 };
 
@@ -258,7 +278,23 @@ UG_DEV void dynamics(S& s, const DevModel& M, const Gp<G>& gp) {
     f3 lin = ld3(s.flin[b]), ang = ld3(s.fang[b]);
     m3 R = ldm(s.fR[b]);
     f3 I = ld3(M.finertia[b]);
-    if (act) {
+    const int anchor = M.fanchor[b];
+    if (act && anchor == 1) {        // hinge (Box-v0 door): gravity torque of the merged COM about the axis, angular damping
+      const f3 ax = ld3(M.faxis[b]);
+      real w = dot(ang, ax);
+      const real tq = dot(ax, cross(mulv(R, ld3(M.fcom[b])), mk3(0, 0, M.fmass[b] * M.gravity)));
+      w += UGP_DT * (tq / M.finertia_axis[b] - w * (UGP_ANG_DAMPING + UGP_ANG_DAMPING * rabs(w)));
+      ang = ax * w; lin = mk3(0, 0, 0);
+      const real ii = 1.0_r / M.finertia_axis[b];
+      real* o = s.fIinv[b];
+      o[0] = ax.x * ax.x * ii; o[1] = ax.x * ax.y * ii; o[2] = ax.x * ax.z * ii; o[3] = ax.y * ax.y * ii; o[4] = ax.y * ax.z * ii; o[5] = ax.z * ax.z * ii;
+    } else if (act && anchor == 2) { // slider (Box-v0 button): gravity and linear damping along the axis, no rotation
+      const f3 ax = ld3(M.faxis[b]);
+      real v = dot(lin, ax);
+      v += UGP_DT * (ax.z * M.gravity - v * (UGP_LIN_DAMPING + UGP_LIN_DAMPING * rabs(v)));
+      lin = ax * v; ang = mk3(0, 0, 0);
+      for (int k = 0; k < 6; k++) s.fIinv[b][k] = 0._r;
+    } else if (act) {
       f3 acc = mk3(0, 0, M.gravity) - lin * (UGP_LIN_DAMPING + UGP_LIN_DAMPING * norm3(lin));
       f3 wl = tmulv(R, ang);
       f3 Iwl = mk3(I.x * wl.x, I.y * wl.y, I.z * wl.z);

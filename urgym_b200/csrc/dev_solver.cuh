@@ -77,6 +77,29 @@ __device__ __noinline__ void collide(S& s, const DevModel& M, const Gp<G> gp) {
   }
   gp.sync();
   int base = 0;
+  // joint rows of the anchored bodies (Box-v0 only), in the checker's order: per body lower limit, upper limit (when violated), motor
+  if (M.fanchor[0] | M.fanchor[1] | M.fanchor[2]) {
+    if (l == 0) {
+#pragma unroll 1
+      for (int b = 0; b < M.nfree; b++) {
+        const int an = M.fanchor[b];
+        if (an == 0 || !(s.flags & (FL_BODY0 << b))) continue;
+        const real qa = anchor_q(s, M, b);
+        const f3 ax = ld3(M.faxis[b]);
+#pragma unroll 1
+        for (int k = 0; k < 3; k++) {
+          real pen = k == 0 ? qa - M.flower[b] : (k == 1 ? M.fupper[b] - qa : qa);
+          if (k < 2 ? pen > 0._r : !(M.fmotor[b] > 0._r)) continue;
+          Con& c = s.con[base++];
+          c.shapes = UG_PSEUDO | (k < 2 ? 1 : 2) | (an == 1 ? 4 : 0); c.bodies = b + 1;
+          st3(c.pa, mk3(0, 0, 0)); st3(c.rb, mk3(0, 0, 0)); st3(c.n, k == 1 ? -ax : ax);
+          c.dist = pen; c.mu = 0._r; c.rest = M.fmotor[b]; c.roll = 0._r;
+        }
+      }
+    }
+    base = gp.shfl(base, 0);
+  }
+  if (l == 0) s.npseudo = base;
 #pragma unroll 1
   for (int i0 = 0; i0 < nnear; i0 += G) {
     int n = 0, sa = 0, sb = 0, p = 0;
@@ -206,7 +229,7 @@ UG_DEV void build_crow(const S& s, const DevModel& M, int desc, CRow& r, bool ro
   const Con& c = s.con[k];
   f3 n = ld3(c.n), t1, t2; plane_space(n, t1, t2);
   f3 dv = type == RT_NORMAL ? n : (dir == 0 ? t1 : t2);
-  const bool lin = type != RT_ROLL;
+  const bool lin = type != RT_ROLL && (c.shapes & (UG_PSEUDO | 4)) != (UG_PSEUDO | 4);
   const int bod = c.bodies;
   r.fa = (bod & 255) - 1; r.fb = ((bod >> 8) & 255) - 1;
   const int ra = ((bod >> 16) & 255) - 1;
@@ -374,18 +397,28 @@ __device__ __noinline__ real solve_and_integrate(S& s, const DevModel& M, const 
         for (int gi = 0; gi < 5; gi++) Er[12 + gi] = Br[6] + c_gear_ratio[gi] * Br[7 + gi];
         if (r.fa >= 0) {
           const real* v = s.vstar + UG_NDOF + 6 * r.fa;
-          dn += dot(r.JlA, r.JlA) * (1.0_r / M.fmass[r.fa]) + dot(r.JaA, symv(s.fIinv[r.fa], r.JaA));
+          if (M.fanchor[r.fa] == 0) dn += dot(r.JlA, r.JlA) * (1.0_r / M.fmass[r.fa]) + dot(r.JaA, symv(s.fIinv[r.fa], r.JaA));
+          else dn += dot(r.JlA, lin_inv(M, r.fa, r.JlA)) + dot(r.JaA, symv(s.fIinv[r.fa], r.JaA));
           rel += dot(r.JlA, ld3(v)) + dot(r.JaA, ld3(v + 3));
         }
         if (r.fb >= 0) {
           const real* v = s.vstar + UG_NDOF + 6 * r.fb;
-          dn += dot(r.JlB, r.JlB) * (1.0_r / M.fmass[r.fb]) + dot(r.JaB, symv(s.fIinv[r.fb], r.JaB));
+          if (M.fanchor[r.fb] == 0) dn += dot(r.JlB, r.JlB) * (1.0_r / M.fmass[r.fb]) + dot(r.JaB, symv(s.fIinv[r.fb], r.JaB));
+          else dn += dot(r.JlB, lin_inv(M, r.fb, r.JlB)) + dot(r.JaB, symv(s.fIinv[r.fb], r.JaB));
           rel += dot(r.JlB, ld3(v)) + dot(r.JaB, ld3(v + 3));
         }
-        const real inv = 1.0_r / dn;
+        real inv = 1.0_r / dn;
+        if (!(dn > 1e-20_r)) inv = 0._r;   // a row no body can move along (a tangent across a hinge axis) stays inert
         p0.y = inv; p0.z = dn;
         const Con& cn = s.con[k];
-        if (type == RT_NORMAL) {
+        if (type == RT_NORMAL && (cn.shapes & UG_PSEUDO)) {
+          if (cn.shapes & 1) {   // joint limit of an anchored body: the robot's limit row formula
+            p0.x = (-cn.dist * UGP_ERP * UGP_INV_DT - rel) * inv; p0.w = 0._r; p1.x = UGP_LIMIT_MAX_IMPULSE;
+          } else {               // position motor to coordinate 0 (cn.dist = coordinate, cn.rest = force limit)
+            const real want = UGP_MOTOR_KP * (0._r - cn.dist) * UGP_INV_DT + (1.0_r - UGP_MOTOR_KD) * rel;
+            p0.x = (want - rel) * inv; p0.w = -cn.rest * UGP_DT; p1.x = cn.rest * UGP_DT;
+          }
+        } else if (type == RT_NORMAL) {
           real pen = cn.dist + UGP_LINEAR_SLOP, rest = 0._r;
           if (rabs(rel) >= UGP_RESTITUTION_VEL_THRESHOLD) rest = rmax(cn.rest * -rel, 0._r);
           real pos_e = 0._r, vel_e = rest - rel;
@@ -429,8 +462,8 @@ __device__ __noinline__ real solve_and_integrate(S& s, const DevModel& M, const 
       build_crow(s, M, dsc, r, true);
 #pragma unroll
       for (int b = 0; b < UG_MAXFREE; b++) {
-        if (r.fa == b) { dl[b] = r.JlA * (1.0_r / M.fmass[b]); da[b] = symv(s.fIinv[b], r.JaA); }
-        if (r.fb == b) { dl[b] = r.JlB * (1.0_r / M.fmass[b]); da[b] = symv(s.fIinv[b], r.JaB); }
+        if (r.fa == b) { dl[b] = M.fanchor[b] == 0 ? r.JlA * (1.0_r / M.fmass[b]) : lin_inv(M, b, r.JlA); da[b] = symv(s.fIinv[b], r.JaA); }
+        if (r.fb == b) { dl[b] = M.fanchor[b] == 0 ? r.JlB * (1.0_r / M.fmass[b]) : lin_inv(M, b, r.JlB); da[b] = symv(s.fIinv[b], r.JaB); }
       }
     }
     const int cmax = min(Rc, so * G + G);
@@ -443,18 +476,19 @@ __device__ __noinline__ real solve_and_integrate(S& s, const DevModel& M, const 
         const Con& cn = s.con[dp & 255];
         f3 n = ld3(cn.n), t1, t2; plane_space(n, t1, t2);
         f3 dv = tp == RT_NORMAL ? n : ((dp >> 12) == 0 ? t1 : t2);
+        const bool angrow = tp == RT_ROLL || (cn.shapes & (UG_PSEUDO | 4)) == (UG_PSEUDO | 4);
         const real* Ep = s.E + (UG_NCOL + cp) * UG_NCOL;
 #pragma unroll
         for (int d = 0; d < UG_NDOF; d++) acc += r.Jr[d] * Ep[d];
         const int bod = cn.bodies, fa = (bod & 255) - 1, fb = ((bod >> 8) & 255) - 1;
         if (fa >= 0) {
           f3 a = pick3(da, fa);
-          f3 vel = tp == RT_ROLL ? a : pick3(dl, fa) + cross(a, ld3(cn.pa));
+          f3 vel = angrow ? a : pick3(dl, fa) + cross(a, ld3(cn.pa));
           acc += dot(dv, vel);
         }
         if (fb >= 0) {
           f3 a = pick3(da, fb);
-          f3 vel = tp == RT_ROLL ? a : pick3(dl, fb) + cross(a, ld3(cn.rb));
+          f3 vel = angrow ? a : pick3(dl, fb) + cross(a, ld3(cn.rb));
           acc -= dot(dv, vel);
         }
       }
@@ -711,7 +745,9 @@ __device__ __noinline__ real solve_and_integrate(S& s, const DevModel& M, const 
     if (b < M.nfree && (s.flags & (FL_BODY0 << b))) {
       const real* vb = s.vstar + UG_NDOF + 6 * b;
       real im = 1.0_r / M.fmass[b];
-      f3 lin = ld3(vb) + pick3(gl, b) * im;
+      f3 lin;
+      if (M.fanchor[b] == 0) lin = ld3(vb) + pick3(gl, b) * im;
+      else lin = ld3(vb) + lin_inv(M, b, pick3(gl, b));
       f3 ang = ld3(vb + 3) + symv(s.fIinv[b], pick3(ga, b));
       st3(s.flin[b], lin); st3(s.fang[b], ang);
       st3(s.fpos[b], ld3(s.fpos[b]) + lin * UGP_DT);

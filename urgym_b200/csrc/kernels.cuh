@@ -7,8 +7,8 @@
 // in the action mapping and the observation only (env_cubes_push_diff_v0.py:209-211,
 // env_golf_joints_v0.py:60-63,85,123-124,229-234).
 template <int ENVF> struct Scene { static constexpr int value = ENVF == 5 ? 2 : (ENVF == 6 ? 4 : ENVF); };
-template <int ENVF> struct ObsDim { static constexpr int value = ENVF == 0 ? 6 : (ENVF == 3 ? 17 : (ENVF == 6 ? 15 : 9)); };
-template <int ENVF> struct ActDim { static constexpr int value = ENVF == 3 ? 9 : (ENVF == 6 ? 6 : 3); };
+template <int ENVF> struct ObsDim { static constexpr int value = ENVF == 0 ? 6 : (ENVF == 3 ? 17 : (ENVF == 6 ? 15 : (ENVF == 7 ? 7 : 9))); };
+template <int ENVF> struct ActDim { static constexpr int value = ENVF == 3 ? 9 : (ENVF == 6 ? 6 : (ENVF == 7 ? 8 : 3)); };
 
 // One out-of-line copy per env type (three call sites; the ball scenes' Euler conversion alone is ~0.9 k instructions):
 // once-per-step straight-line code is what the instruction caches miss on.
@@ -38,6 +38,9 @@ __device__ __noinline__ void observe(S& s, const DevModel& M, real* o, real* o2,
     v[9] = gripper_opening(s, M);
     v[10] = s.fpos[0][0]; v[11] = s.fpos[0][1]; v[12] = s.fpos[0][2];
     v[13] = s.fquat[0][0]; v[14] = s.fquat[0][1]; v[15] = s.fquat[0][2]; v[16] = s.fquat[0][3];
+  } else if (ENV == 7) {                // env_box_v0.py:161-170: end-effector position and quaternion
+    q4 eq = link_quat_chain(s.q, M, 7);
+    v[0] = ep.x; v[1] = ep.y; v[2] = ep.z; v[3] = eq.x; v[4] = eq.y; v[5] = eq.z; v[6] = eq.w;
   } else {
     f3 st = club_foot(s), b = ld3(s.fpos[1]), h = mk3(0._r, -0.6_r, 0.02_r);
     f3 d1 = st - b, d2 = h - b;
@@ -67,7 +70,7 @@ __device__ __noinline__ void observe(S& s, const DevModel& M, real* o, real* o2,
 // the fp64 build showed that those ticks alone changed trip counts against the uncapped checker, so it gets 24; the Golf scenes (club in the fingers and on the pitch) exceed 24 on 2.5-3.5 % and 32 on
 // 0.07-1 %. Rolling friction exists in the Golf scenes only (<= 3 manifolds seen, 4 kept). Rows = 3 per point (normal +
 // friction pair) + 2 per rolling manifold. Ticks that exceed a capacity are counted (urgym_stats out[6]).
-template <int ENVF> struct EnvNC { static constexpr int value = Scene<ENVF>::value == 4 ? 32 : (Scene<ENVF>::value == 2 ? 24 : 20); };
+template <int ENVF> struct EnvNC { static constexpr int value = Scene<ENVF>::value == 4 ? 32 : ((Scene<ENVF>::value == 2 || Scene<ENVF>::value == 7) ? 24 : 20); };  // Box-v0: 20 + its 5 joint rows
 template <int ENVF> struct EnvRC { static constexpr int value = 3 * EnvNC<ENVF>::value + (Scene<ENVF>::value == 4 ? 8 : 0); };
 template <int ENVF> using EnvSmem = SmemT<EnvNC<ENVF>::value, EnvRC<ENVF>::value>;
 
@@ -116,6 +119,11 @@ __global__ void __launch_bounds__(32, UG_MIN_CTAS) env_kernel(KParams P) {
       for (int i = 0; i < 6; i++) t[i] = s.q[i] + a[i];
       gp.sync();
       set_arm_targets(s, t, lane);
+    } else if (ENV == 7) {               // env_box_v0.py:124-126: pose (position + quaternion) + action[:7] component-wise, gripper length
+      q4 eq = link_quat_chain(s.q, M, 7);
+      move_ee(s, M, ep + mk3(a[0], a[1], a[2]), mkq(eq.x + a[3], eq.y + a[4], eq.z + a[5], eq.w + a[6]), gp);
+      move_gripper(s, a[7], lane);
+      limit = 120;                       // env_box_v0.py:127-128: a fixed 120 ticks instead of wait_until_stable
     } else if (ENV == 2 || ENV == 4) {   // env_cubes_push_v0.py:122-126, env_golf_v0.py:122-126
       move_ee(s, M, ep + mk3(a[0], a[1], a[2]), vert, gp);
     } else {                              // env_cubes_grasp_v0.py:121-144
@@ -162,7 +170,7 @@ __global__ void __launch_bounds__(32, UG_MIN_CTAS) env_kernel(KParams P) {
       moved = tick<G, RC>(s, M, gp, &iters);
     }
     n++; tick_total++;
-    bool done = phase == PH_ARM10 || phase == PH_RAW ? n >= limit : (moved < UGP_SETTLE_THRESHOLD || n >= limit);
+    bool done = phase == PH_ARM10 || phase == PH_RAW || ENV == 7 ? n >= limit : (moved < UGP_SETTLE_THRESHOLD || n >= limit);
     if (!done) continue;
     if (phase == PH_RAW) break;
     fk_bodies(s, M, gp);
@@ -205,6 +213,15 @@ __global__ void __launch_bounds__(32, UG_MIN_CTAS) env_kernel(KParams P) {
         } else if (grasp_now && s.fpos[0][2] > 0.2_r) { rew += 10._r; term = true; succ = true; }
         if (lane == 0) s.flags = fl;
         rew -= 0.1_r;
+      } else if (ENV == 7) {               // env_box_v0.py:141-159 (button_touch_mode='any'), :129-137; sticky bits as in CubesGrasp
+        const real door = anchor_q(s, M, 0), button = anchor_q(s, M, 1);
+        int fl = s.flags;
+        gp.sync();
+        if (!(fl & FL_APPROACHED)) { if (door > 1.9_r) { fl |= FL_APPROACHED; rew = 1._r; } }      // box_opened
+        else if (!(fl & FL_GRASPED)) { if (button < -0.02_r) { fl |= FL_GRASPED; rew = 1._r; } }   // button_pressed
+        else if (door < 0.1_r) { rew = 1._r; term = true; succ = true; }                            // box_closed
+        if (lane == 0) s.flags = fl;
+        rew -= 0.1_r;
       } else {                             // env_golf_v0.py:130-183
         f3 hole = mk3(0._r, -0.6_r, 0.02_r), ball = ld3(s.fpos[1]);
         bool in_fingers = touch_robot(s, M, 9, 18, 1, -1);
@@ -223,8 +240,9 @@ __global__ void __launch_bounds__(32, UG_MIN_CTAS) env_kernel(KParams P) {
       step_count++; ep_ret += rew;
       trunc = step_count >= M.max_steps;
       if (P.contacts) {
-        int nc = P.inject_pairs ? 0 : s.ncon;
-        for (int k = lane; k < UG_MAXC; k += G) { P.contacts[((size_t)env * UG_MAXC + k) * 2] = k < nc ? (s.con[k].shapes & 255) : -1; P.contacts[((size_t)env * UG_MAXC + k) * 2 + 1] = k < nc ? (s.con[k].shapes >> 8) : -1; }
+        const int np0 = P.inject_pairs ? 0 : s.npseudo;   // joint rows of anchored bodies sit at the head of con and are not contacts
+        int nc = P.inject_pairs ? 0 : s.ncon - np0;
+        for (int k = lane; k < UG_MAXC; k += G) { P.contacts[((size_t)env * UG_MAXC + k) * 2] = k < nc ? (s.con[np0 + k].shapes & 255) : -1; P.contacts[((size_t)env * UG_MAXC + k) * 2 + 1] = k < nc ? (s.con[np0 + k].shapes >> 8) : -1; }
         if (lane == 0) P.ccount[env] = nc;
         if (lane < UG_HITWORDS) P.hitmask[(size_t)env * UG_HITWORDS + lane] = s.hit[lane];
       }
@@ -266,6 +284,12 @@ __global__ void __launch_bounds__(32, UG_MIN_CTAS) env_kernel(KParams P) {
         spawn(s, 0, mk3(r * cs, r * sn, 0.1_r), lane);
         move_ee(s, M, ep, link_quat_chain(s.q, M, 7), gp);
         phase = PH_SETTLE2;
+      } else if (ENV == 7) {               // env_box_v0.py:178-185: move_ee to the current pose; reset_box(): both joints to 0
+        move_ee(s, M, ep, link_quat_chain(s.q, M, 7), gp);
+        spawn(s, 0, ld3(M.forigin[0]), lane); spawn(s, 1, ld3(M.forigin[1]), lane);
+        gp.sync();
+        observe<ENVF>(s, M, P.obs + (size_t)OD * env, nullptr, lane);
+        break;
       } else {                             // env_golf_v0.py:238-256
         vert = mkq(0.0_r, 0.0_r, -0.70_r, 0.70_r);
         move_ee(s, M, mk3(0.0_r, -0.60_r, 0.40_r), vert, gp);

@@ -17,7 +17,7 @@
 // the measured distributions, tools/contact_hist.py); UG_MAXC is the width of the contact-point export and the largest of them.
 #define UG_MAXC 32
 #define UG_STATE 96
-#define UG_ENV_COUNT 7  // 0 BallBalance 1 TwoBallsBalance 2 CubesPush 3 CubesGrasp 4 Golf 5 CubesPushDiff 6 GolfJoints
+#define UG_ENV_COUNT 8  // 0 BallBalance 1 TwoBallsBalance 2 CubesPush 3 CubesGrasp 4 Golf 5 CubesPushDiff 6 GolfJoints 7 Box
 
 // Convex polytope of a gripper link whose collision geometry is a mesh (model_data.h: URG_POLYS), in the link frame.
 #define UG_NPOLY 5
@@ -57,6 +57,13 @@ struct DevModel {
   int env_type, nfree, nshapes, npairs, obs_dim, act_dim, max_steps; real gravity;
   int generic_sweeps;  // 1: contact-free ticks take the generic sweeps too (URGYM_GENERIC_SWEEPS=1 at create; comparison runs and tests)
   real fmass[UG_MAXFREE]; real finertia[UG_MAXFREE][3];
+  // A body slot is a free rigid body (fanchor 0) or a world-anchored 1-DoF body of Box-v0's second articulated body
+  // (skew-box-button.urdf: both joints hang off the fixed base): 1 = hinge about the world axis faxis through the body origin
+  // forigin, 2 = slider along faxis from forigin. Generalized inverse inertia: faxis faxis^T / finertia_axis (angular) or
+  // faxis faxis^T / fmass (linear). flower / fupper: joint limits; fcom: hinge body's merged COM (gravity torque); fmotor:
+  // force limit of the slider's position motor to coordinate 0 (env_box_v0.py:176), 0 = none.
+  int fanchor[UG_MAXFREE]; real faxis[UG_MAXFREE][3], forigin[UG_MAXFREE][3], fcom[UG_MAXFREE][3];
+  real finertia_axis[UG_MAXFREE], flower[UG_MAXFREE], fupper[UG_MAXFREE], fmotor[UG_MAXFREE];
   DevShape shapes[UG_MAXSHAPES]; uint8_t pairs[UG_MAXPAIRS][2];
   // broad-phase bound per pair: the pair can only produce manifold points (separating-axis slack <= margin on all 15 axes)
   // while the centre distance (static partner: distance from the centre to the static box) is <= cullr (model_build.cpp)

@@ -60,6 +60,7 @@ int build_model(int env_type_full, DevModel* m) {
   // CubesPushDiff (5) and GolfJoints (6) live in their parents' worlds (env_cubes_push_diff_v0.py, env_golf_joints_v0.py)
   const int env_type = env_type_full == 5 ? 2 : (env_type_full == 6 ? 4 : env_type_full);
   std::memset(m, 0, sizeof(*m));
+  const double base[3] = {0, env_type == 7 ? 0.5 : 0.0, 0};   // robot base: env_box_v0.py:55 (0, 0.5, 0), every other env the origin
   int dof_of_link[UG_NLINK];
   for (int i = 0; i < UG_NLINK; i++) dof_of_link[i] = -1;
   for (int d = 0; d < UG_NDOF; d++) dof_of_link[MOV[d]] = d;
@@ -97,7 +98,7 @@ int build_model(int env_type_full, DevModel* m) {
     D3 jx = {{L.jxyz[0], L.jxyz[1], L.jxyz[2]}}; D3 o = mv(pr, jx);
     DM jr; for (int k = 0; k < 9; k++) jr.m[k] = L.jrot[k];
     DM r = mm(pr, jr);
-    for (int k = 0; k < 3; k++) m->jpos[d][k] = (real)(pp.v[k] + o.v[k]);
+    for (int k = 0; k < 3; k++) m->jpos[d][k] = (real)(pp.v[k] + o.v[k] + (pb < 0 ? base[k] : 0.0));
     for (int k = 0; k < 9; k++) m->jrot[d][k] = (real)r.m[k];
     if (!((L.axis[0] == 1 && L.axis[1] == 0 && L.axis[2] == 0) || (L.axis[0] == 0 && L.axis[1] == 1 && L.axis[2] == 0) || (L.axis[0] == 0 && L.axis[1] == 0 && L.axis[2] == 1))) return -1;
     m->axis[d] = L.axis[0] == 1 ? 0 : (L.axis[1] == 1 ? 1 : 2);
@@ -211,6 +212,26 @@ int build_model(int env_type_full, DevModel* m) {
       m->shapes[ns++] = mk_box(-1, 2, ground_c, ground_h, 1.0);
       break;
     }
+    case 7: {  // Box-v0: env_box_v0.py:55-85, urgym/urdf/skew-box-button.urdf; same shape order as the oracle's make_scene
+      m->nfree = 2; m->obs_dim = 7; m->act_dim = 8; m->max_steps = 200; m->gravity = (real)-10.0;
+      const double mh1 = 0.05, mh3 = 0.1, md = 0.1 + 2 * mh1 + mh3;
+      m->fanchor[0] = 1; m->faxis[0][1] = (real)1; m->forigin[0][0] = (real)0.075; m->forigin[0][2] = (real)0.1; m->flower[0] = (real)0; m->fupper[0] = (real)2;
+      m->finertia_axis[0] = (real)(0.5 + 2 * mh1 * (0.13 * 0.13 + 0.025 * 0.025) + mh3 * (0.13 * 0.13 + 0.05 * 0.05));
+      m->fmass[0] = (real)md; for (int k = 0; k < 3; k++) m->finertia[0][k] = (real)1;
+      m->fcom[0][0] = (real)(-0.13 * (2 * mh1 + mh3) / md); m->fcom[0][2] = (real)((2 * mh1 * 0.025 + mh3 * 0.05) / md);
+      m->fanchor[1] = 2; m->faxis[1][2] = (real)1; m->forigin[1][2] = (real)0.07; m->flower[1] = (real)-0.05; m->fupper[1] = (real)0; m->fmotor[1] = (real)1;
+      m->fmass[1] = (real)0.01; for (int k = 0; k < 3; k++) m->finertia[1][k] = (real)1;
+      const double c0[3] = {-0.076, 0, 0}, h0[3] = {0.08, 0.1, 0.005}, c1[3] = {-0.13, 0.05, 0.025}, c2[3] = {-0.13, -0.05, 0.025}, hp[3] = {0.005, 0.005, 0.025};
+      const double c3[3] = {-0.13, 0, 0.05}, h3[3] = {0.01, 0.05, 0.01}, hb[3] = {0.02, 0.02, 0.025};
+      m->shapes[ns++] = mk_box(1, 0, c0, h0, 0.5); m->shapes[ns++] = mk_box(1, 1, c1, hp, 0.5); m->shapes[ns++] = mk_box(1, 2, c2, hp, 0.5);
+      m->shapes[ns++] = mk_box(1, 3, c3, h3, 1.0); m->shapes[ns++] = mk_box(2, 0, zero, hb, 0.5);
+      const double w1[3] = {0.075, 0, 0.045}, w2[3] = {-0.075, 0, 0.045}, wh[3] = {0.005, 0.1, 0.045}, w3[3] = {0, 0.1, 0.045}, w4[3] = {0, -0.1, 0.045}, wg[3] = {0.075, 0.005, 0.045};
+      m->shapes[ns++] = mk_box(-1, 0, w1, wh, 0.5); m->shapes[ns++] = mk_box(-1, 1, w2, wh, 0.5);
+      m->shapes[ns++] = mk_box(-1, 2, w3, wg, 0.5); m->shapes[ns++] = mk_box(-1, 3, w4, wg, 0.5);
+      const double pc[3] = {0, 0, -5.0}, ph[3] = {15, 15, 5};
+      m->shapes[ns++] = mk_box(-1, 4, pc, ph, 1.0);
+      break;
+    }
   }
   if (env_type_full == 6) { m->obs_dim = 15; m->act_dim = 6; }   // env_golf_joints_v0.py:60-63
   m->nshapes = ns;
@@ -230,9 +251,13 @@ int build_model(int env_type_full, DevModel* m) {
   int np = 0;
   auto add = [&](int a, int b) { if (np < UG_MAXPAIRS) { m->pairs[np][0] = (uint8_t)a; m->pairs[np][1] = (uint8_t)b; } np++; };
   for (int a = 0; a < ns; a++) for (int b = a + 1; b < ns; b++) if (m->shapes[a].body > 0 && m->shapes[b].body > 0 && m->shapes[a].body != m->shapes[b].body) add(a, b);
-  for (int a = 0; a < ns; a++) for (int b = 0; b < ns; b++) if (m->shapes[a].body > 0 && m->shapes[b].body < 0) add(a, b);
-  for (int a = 0; a < ns; a++) for (int b = 0; b < ns; b++) if (m->shapes[a].body == 0 && m->shapes[b].body > 0) add(a, b);
-  for (int a = 0; a < ns; a++) for (int b = 0; b < ns; b++) if (m->shapes[a].body == 0 && m->shapes[b].body < 0) add(a, b);
+  // Box-v0 (pair budget): door and button never reach the ground plane (static id 4); the upper arm links (the last four robot
+  // shapes: 4, 3, 2, 1) are tested against the ground plane only — same rules as the oracle's make_scene
+  auto plane7 = [&](int b) { return env_type == 7 && m->shapes[b].body < 0 && m->shapes[b].link == 4; };
+  auto arm_only = [&](int a, int b) { return env_type == 7 && a >= 13 && !plane7(b); };
+  for (int a = 0; a < ns; a++) for (int b = 0; b < ns; b++) if (m->shapes[a].body > 0 && m->shapes[b].body < 0 && !plane7(b)) add(a, b);
+  for (int a = 0; a < ns; a++) for (int b = 0; b < ns; b++) if (m->shapes[a].body == 0 && m->shapes[b].body > 0 && !arm_only(a, b)) add(a, b);
+  for (int a = 0; a < ns; a++) for (int b = 0; b < ns; b++) if (m->shapes[a].body == 0 && m->shapes[b].body < 0 && !arm_only(a, b)) add(a, b);
   if (np > UG_MAXPAIRS) return -1;
   m->npairs = np;
   // Broad-phase bound per pair. The narrowphase reports a box-box manifold when the separating-axis slack is <= margin on

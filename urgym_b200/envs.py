@@ -1,5 +1,5 @@
-"""Host-side mirror of the reference's Gymnasium interface for the in-scope envs (the five of the
-north star plus the two variants CubesPushDiff and GolfJoints).
+"""Host-side mirror of the reference's Gymnasium interface for every env it registers (the five of the
+north star, the two variants CubesPushDiff and GolfJoints, and Box).
 
 Reference: /root/reference/urgym/envs/__init__.py:1-50 (ids, max_episode_steps) and the env classes, e.g.
 /root/reference/urgym/envs/env_ball_balance_v0.py:34-173 (`__init__(camera=None, reward_type='dense',
@@ -25,11 +25,11 @@ from ._lib import ENV_TYPES
 
 try:  # the reference depends on gymnasium==0.29.1 (setup.py:9); it is optional here
     import gymnasium as _gym
-    from gymnasium.spaces import Box
+    from gymnasium.spaces import Box as BoxSpace
 except Exception:  # minimal stand-in used only when gymnasium cannot be imported
     _gym = None
 
-    class Box:
+    class BoxSpace:
         def __init__(self, low, high, dtype=np.float32):
             self.low = np.asarray(low, dtype=dtype); self.high = np.asarray(high, dtype=dtype)
             self.dtype = np.dtype(dtype); self.shape = self.low.shape
@@ -60,16 +60,18 @@ SPECS = {
     # variants: same world, other observation / action mapping (env_cubes_push_diff_v0.py:209-211, env_golf_joints_v0.py:60-63)
     'URGym/CubesPushDiff-v0': ('CubesPushDiff', 50, ([-1.0] * 9, [1.0] * 9), ([-0.1] * 3, [0.1] * 3)),
     'URGym/GolfJoints-v0': ('GolfJoints', 100, ([-2 * PI] * 6 + [-1.0] * 9, [2 * PI] * 6 + [1.0] * 9), ([-0.1] * 6, [0.1] * 6)),
+    # env_box_v0.py:40-44 (observation: end-effector position + quaternion; action: pose increment + gripper opening length);
+    # max_episode_steps 200 (urgym/envs/__init__.py:3-8)
+    'URGym/Box-v0': ('Box', 200, ([-1.0] * 3 + [-PI] * 4, [1.0] * 3 + [PI] * 4), ([-0.05] * 3 + [-PI / 10] * 4 + [0.0], [0.05] * 3 + [PI / 10] * 4 + [0.085])),
 }
-# registered by the reference but outside this backend's scope
-UNSUPPORTED = ('URGym/Box-v0',)
-HAS_SUCCESS_INFO = ('CubesPush', 'CubesGrasp', 'Golf', 'CubesPushDiff', 'GolfJoints')  # info={'is_success': ...} (env_cubes_push_v0.py:143 etc.)
+UNSUPPORTED = ()   # every id the reference registers is backed
+HAS_SUCCESS_INFO = ('CubesPush', 'CubesGrasp', 'Golf', 'CubesPushDiff', 'GolfJoints', 'Box')  # info={'is_success': ...} (env_cubes_push_v0.py:143 etc.)
 
 
 def _spaces(env_id):
     _, _, (ol, oh), (al, ah) = SPECS[env_id]
-    return (Box(low=np.array(ol, dtype=np.float64), high=np.array(oh, dtype=np.float64), dtype=np.float64),
-            Box(low=np.array(al, dtype=np.float32), high=np.array(ah, dtype=np.float32), dtype=np.float32))
+    return (BoxSpace(low=np.array(ol, dtype=np.float64), high=np.array(oh, dtype=np.float64), dtype=np.float64),
+            BoxSpace(low=np.array(al, dtype=np.float32), high=np.array(ah, dtype=np.float32), dtype=np.float32))
 
 
 class URGymVectorEnv:
@@ -166,7 +168,21 @@ CubesGrasp = _mk('URGym/CubesGrasp-v0')
 Golf = _mk('URGym/Golf-v0')
 CubesPushDiff = _mk('URGym/CubesPushDiff-v0')
 GolfJoints = _mk('URGym/GolfJoints-v0')
-_CLASSES = {c.env_id: c for c in (BallBalance, TwoBallsBalance, CubesPush, CubesGrasp, Golf, CubesPushDiff, GolfJoints)}
+
+
+class Box(_SingleEnv):
+    """urgym_b200 backend of URGym/Box-v0 (env_box_v0.py:21: `BoxManipulation(button_touch_mode='any', camera=None, render_mode='human')`).
+    Only the registered default button_touch_mode='any' is backed (the button counts as pressed whoever pushed it down)."""
+    env_id = 'URGym/Box-v0'
+
+    def __init__(self, button_touch_mode='any', camera=None, render_mode='human', device=0, seed=None):
+        if button_touch_mode != 'any':
+            raise NotImplementedError("button_touch_mode=%r: only 'any' (the registered default, urgym/envs/__init__.py:7) is backed" % (button_touch_mode,))
+        super().__init__(camera=camera, render_mode=render_mode, device=device, seed=seed)
+
+
+BoxManipulation = Box
+_CLASSES = {c.env_id: c for c in (BallBalance, TwoBallsBalance, CubesPush, CubesGrasp, Golf, CubesPushDiff, GolfJoints, Box)}
 
 
 def make(env_id, **kwargs):
