@@ -305,11 +305,11 @@ def test_env_logic_matches_reference_fixture(name, reward_type):
 
 
 # ------------------------------------------------------------------------------------------ full-size properties
-@pytest.mark.parametrize('name,n', [('BallBalance', 4096), ('TwoBallsBalance', 16384), ('CubesPush', 16384), ('CubesGrasp', 16384), ('Golf', 4096)])
+@pytest.mark.parametrize('name,n', [('BallBalance', 4096), ('TwoBallsBalance', 16384), ('CubesPush', 16384), ('CubesGrasp', 16384), ('Golf', 4096), ('Box', 4096)])
 def test_full_size_run_properties(name, n):
     gb = _batch(name, n, seed=11)
     gb.reset()
-    assert int(_np(gb.reset_ticks).min()) >= 11
+    assert int(_np(gb.reset_ticks).min()) >= (10 if name == 'Box' else 11)
     rng = np.random.default_rng(3)
     steps = 22 if name == 'CubesGrasp' else 8
     ended = 0; tick_sum = int(_np(gb.reset_ticks).astype(np.int64).sum())
@@ -330,6 +330,11 @@ def test_full_size_run_properties(name, n):
             assert trunc.bool()[~restarted_early].all()                                 # TimeLimit: 20 steps
     st = gb.get_state()
     assert torch.isfinite(st).all()
+    if name == 'Box':                                                                   # anchored bodies stay on their joints and within their limits
+        assert (gb.nticks[:, 0] == 120).all()
+        assert (st[:, 38:41] - torch.tensor([0.075, 0.0, 0.1], device=st.device)).abs().max() < 1e-6 and st[:, 51:53].abs().max() < 1e-6
+        door = 2 * torch.atan2(st[:, 42], st[:, 44]); button = st[:, 53] - 0.07
+        assert st[:, [41, 43]].abs().max() < 1e-6 and door.min() > -0.02 and door.max() < 2.02 and button.min() > -0.052 and button.max() < 2e-3
     fl = st[:, 31].to(torch.int64)
     for b in range(3):
         act = (fl & (16 << b)) != 0

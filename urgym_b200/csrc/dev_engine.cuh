@@ -24,9 +24,12 @@ struct Con {
   real dist, mu, rest, roll;
 };
 
-template <int NCAP, int RC>
+template <int NCAP, int RC, bool ANCH = false>
 struct SmemT {
   static constexpr int NC_CAP = NCAP;  // manifold points kept per tick
+  // the scene has world-anchored 1-DoF bodies (Box-v0's door and button): every branch that serves them is compiled under this flag,
+  // so the kernels of the other scenes carry none of it (same instructions, same bits as before Box-v0 existed)
+  static constexpr bool ANCHORS = ANCH;
   static constexpr int TTRI = RC * (RC + 1) / 2;  // packed lower triangle of the symmetric contact block
   // ---- state that lives across the ticks of one gym step
   real q[UG_NDOF], qd[UG_NDOF], tgt[8];
@@ -278,7 +281,7 @@ UG_DEV void dynamics(S& s, const DevModel& M, const Gp<G>& gp) {
     f3 lin = ld3(s.flin[b]), ang = ld3(s.fang[b]);
     m3 R = ldm(s.fR[b]);
     f3 I = ld3(M.finertia[b]);
-    const int anchor = M.fanchor[b];
+    const int anchor = S::ANCHORS ? M.fanchor[b] : 0;
     if (act && anchor == 1) {        // hinge (Box-v0 door): gravity torque of the merged COM about the axis, angular damping
       const f3 ax = ld3(M.faxis[b]);
       real w = dot(ang, ax);

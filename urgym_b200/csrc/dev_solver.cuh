@@ -78,7 +78,7 @@ __device__ __noinline__ void collide(S& s, const DevModel& M, const Gp<G> gp) {
   gp.sync();
   int base = 0;
   // joint rows of the anchored bodies (Box-v0 only), in the checker's order: per body lower limit, upper limit (when violated), motor
-  if (M.fanchor[0] | M.fanchor[1] | M.fanchor[2]) {
+  if constexpr (S::ANCHORS) {
     if (l == 0) {
 #pragma unroll 1
       for (int b = 0; b < M.nfree; b++) {
@@ -99,7 +99,7 @@ __device__ __noinline__ void collide(S& s, const DevModel& M, const Gp<G> gp) {
     }
     base = gp.shfl(base, 0);
   }
-  if (l == 0) s.npseudo = base;
+  if (l == 0) s.npseudo = base;   // 0 unless S::ANCHORS
 #pragma unroll 1
   for (int i0 = 0; i0 < nnear; i0 += G) {
     int n = 0, sa = 0, sb = 0, p = 0;
@@ -229,7 +229,7 @@ UG_DEV void build_crow(const S& s, const DevModel& M, int desc, CRow& r, bool ro
   const Con& c = s.con[k];
   f3 n = ld3(c.n), t1, t2; plane_space(n, t1, t2);
   f3 dv = type == RT_NORMAL ? n : (dir == 0 ? t1 : t2);
-  const bool lin = type != RT_ROLL && (c.shapes & (UG_PSEUDO | 4)) != (UG_PSEUDO | 4);
+  const bool lin = type != RT_ROLL && (!S::ANCHORS || (c.shapes & (UG_PSEUDO | 4)) != (UG_PSEUDO | 4));
   const int bod = c.bodies;
   r.fa = (bod & 255) - 1; r.fb = ((bod >> 8) & 255) - 1;
   const int ra = ((bod >> 16) & 255) - 1;
@@ -397,21 +397,21 @@ __device__ __noinline__ real solve_and_integrate(S& s, const DevModel& M, const 
         for (int gi = 0; gi < 5; gi++) Er[12 + gi] = Br[6] + c_gear_ratio[gi] * Br[7 + gi];
         if (r.fa >= 0) {
           const real* v = s.vstar + UG_NDOF + 6 * r.fa;
-          if (M.fanchor[r.fa] == 0) dn += dot(r.JlA, r.JlA) * (1.0_r / M.fmass[r.fa]) + dot(r.JaA, symv(s.fIinv[r.fa], r.JaA));
+          if (!S::ANCHORS || M.fanchor[r.fa] == 0) dn += dot(r.JlA, r.JlA) * (1.0_r / M.fmass[r.fa]) + dot(r.JaA, symv(s.fIinv[r.fa], r.JaA));
           else dn += dot(r.JlA, lin_inv(M, r.fa, r.JlA)) + dot(r.JaA, symv(s.fIinv[r.fa], r.JaA));
           rel += dot(r.JlA, ld3(v)) + dot(r.JaA, ld3(v + 3));
         }
         if (r.fb >= 0) {
           const real* v = s.vstar + UG_NDOF + 6 * r.fb;
-          if (M.fanchor[r.fb] == 0) dn += dot(r.JlB, r.JlB) * (1.0_r / M.fmass[r.fb]) + dot(r.JaB, symv(s.fIinv[r.fb], r.JaB));
+          if (!S::ANCHORS || M.fanchor[r.fb] == 0) dn += dot(r.JlB, r.JlB) * (1.0_r / M.fmass[r.fb]) + dot(r.JaB, symv(s.fIinv[r.fb], r.JaB));
           else dn += dot(r.JlB, lin_inv(M, r.fb, r.JlB)) + dot(r.JaB, symv(s.fIinv[r.fb], r.JaB));
           rel += dot(r.JlB, ld3(v)) + dot(r.JaB, ld3(v + 3));
         }
         real inv = 1.0_r / dn;
-        if (!(dn > 1e-20_r)) inv = 0._r;   // a row no body can move along (a tangent across a hinge axis) stays inert
+        if (S::ANCHORS && !(dn > 1e-20_r)) inv = 0._r;   // a row no body can move along (a tangent across a hinge axis) stays inert
         p0.y = inv; p0.z = dn;
         const Con& cn = s.con[k];
-        if (type == RT_NORMAL && (cn.shapes & UG_PSEUDO)) {
+        if (S::ANCHORS && type == RT_NORMAL && (cn.shapes & UG_PSEUDO)) {
           if (cn.shapes & 1) {   // joint limit of an anchored body: the robot's limit row formula
             p0.x = (-cn.dist * UGP_ERP * UGP_INV_DT - rel) * inv; p0.w = 0._r; p1.x = UGP_LIMIT_MAX_IMPULSE;
           } else {               // position motor to coordinate 0 (cn.dist = coordinate, cn.rest = force limit)
@@ -462,8 +462,8 @@ __device__ __noinline__ real solve_and_integrate(S& s, const DevModel& M, const 
       build_crow(s, M, dsc, r, true);
 #pragma unroll
       for (int b = 0; b < UG_MAXFREE; b++) {
-        if (r.fa == b) { dl[b] = M.fanchor[b] == 0 ? r.JlA * (1.0_r / M.fmass[b]) : lin_inv(M, b, r.JlA); da[b] = symv(s.fIinv[b], r.JaA); }
-        if (r.fb == b) { dl[b] = M.fanchor[b] == 0 ? r.JlB * (1.0_r / M.fmass[b]) : lin_inv(M, b, r.JlB); da[b] = symv(s.fIinv[b], r.JaB); }
+        if (r.fa == b) { dl[b] = (!S::ANCHORS || M.fanchor[b] == 0) ? r.JlA * (1.0_r / M.fmass[b]) : lin_inv(M, b, r.JlA); da[b] = symv(s.fIinv[b], r.JaA); }
+        if (r.fb == b) { dl[b] = (!S::ANCHORS || M.fanchor[b] == 0) ? r.JlB * (1.0_r / M.fmass[b]) : lin_inv(M, b, r.JlB); da[b] = symv(s.fIinv[b], r.JaB); }
       }
     }
     const int cmax = min(Rc, so * G + G);
@@ -476,7 +476,7 @@ __device__ __noinline__ real solve_and_integrate(S& s, const DevModel& M, const 
         const Con& cn = s.con[dp & 255];
         f3 n = ld3(cn.n), t1, t2; plane_space(n, t1, t2);
         f3 dv = tp == RT_NORMAL ? n : ((dp >> 12) == 0 ? t1 : t2);
-        const bool angrow = tp == RT_ROLL || (cn.shapes & (UG_PSEUDO | 4)) == (UG_PSEUDO | 4);
+        const bool angrow = tp == RT_ROLL || (S::ANCHORS && (cn.shapes & (UG_PSEUDO | 4)) == (UG_PSEUDO | 4));
         const real* Ep = s.E + (UG_NCOL + cp) * UG_NCOL;
 #pragma unroll
         for (int d = 0; d < UG_NDOF; d++) acc += r.Jr[d] * Ep[d];
@@ -746,7 +746,7 @@ __device__ __noinline__ real solve_and_integrate(S& s, const DevModel& M, const 
       const real* vb = s.vstar + UG_NDOF + 6 * b;
       real im = 1.0_r / M.fmass[b];
       f3 lin;
-      if (M.fanchor[b] == 0) lin = ld3(vb) + pick3(gl, b) * im;
+      if (!S::ANCHORS || M.fanchor[b] == 0) lin = ld3(vb) + pick3(gl, b) * im;
       else lin = ld3(vb) + lin_inv(M, b, pick3(gl, b));
       f3 ang = ld3(vb + 3) + symv(s.fIinv[b], pick3(ga, b));
       st3(s.flin[b], lin); st3(s.fang[b], ang);

@@ -72,7 +72,7 @@ __device__ __noinline__ void observe(S& s, const DevModel& M, real* o, real* o2,
 // friction pair) + 2 per rolling manifold. Ticks that exceed a capacity are counted (urgym_stats out[6]).
 template <int ENVF> struct EnvNC { static constexpr int value = Scene<ENVF>::value == 4 ? 32 : ((Scene<ENVF>::value == 2 || Scene<ENVF>::value == 7) ? 24 : 20); };  // Box-v0: 20 + its 5 joint rows
 template <int ENVF> struct EnvRC { static constexpr int value = 3 * EnvNC<ENVF>::value + (Scene<ENVF>::value == 4 ? 8 : 0); };
-template <int ENVF> using EnvSmem = SmemT<EnvNC<ENVF>::value, EnvRC<ENVF>::value>;
+template <int ENVF> using EnvSmem = SmemT<EnvNC<ENVF>::value, EnvRC<ENVF>::value, Scene<ENVF>::value == 7>;
 
 template <int ENVF, int G>
 __global__ void __launch_bounds__(32, UG_MIN_CTAS) env_kernel(KParams P) {
@@ -240,7 +240,7 @@ __global__ void __launch_bounds__(32, UG_MIN_CTAS) env_kernel(KParams P) {
       step_count++; ep_ret += rew;
       trunc = step_count >= M.max_steps;
       if (P.contacts) {
-        const int np0 = P.inject_pairs ? 0 : s.npseudo;   // joint rows of anchored bodies sit at the head of con and are not contacts
+        const int np0 = (!S::ANCHORS || P.inject_pairs) ? 0 : s.npseudo;   // joint rows of anchored bodies sit at the head of con and are not contacts
         int nc = P.inject_pairs ? 0 : s.ncon - np0;
         for (int k = lane; k < UG_MAXC; k += G) { P.contacts[((size_t)env * UG_MAXC + k) * 2] = k < nc ? (s.con[np0 + k].shapes & 255) : -1; P.contacts[((size_t)env * UG_MAXC + k) * 2 + 1] = k < nc ? (s.con[np0 + k].shapes >> 8) : -1; }
         if (lane == 0) P.ccount[env] = nc;
