@@ -101,3 +101,17 @@ def test_box_model_facts():
     assert abs(d - 2.0) < 5e-3 and abs(b) < 1e-4          # past 90 degrees the door falls open; the button returns
     d, b = run(1.2, 0.0, steps=14)
     assert abs(d) < 5e-3                                   # below it the door falls shut (onto the button and its limit)
+
+
+def test_scripted_policy_solves_the_task_on_the_oracle():
+    """tests/scripted_box.py: grasp the handle bar, lift the door along its arc past 1.9 rad (+1), let go, press the button with
+    the closed gripper (+1), push the door back over its tipping point so that it falls shut (+1, terminated, is_success) — all
+    through the physics, inside the 200-step limit."""
+    import scripted_box as SB
+    ob = O.OracleBatch('Box', 1, seed=1)
+    ob.reset()
+    log = SB.run(lambda a: ob.step(a), 1)
+    wins = [k for k, r in enumerate(log) if r['reward'][0] > 0.5]
+    assert len(wins) == 3 and len(log) < 200, (wins, len(log))
+    assert log[-1]['terminated'][0] and log[-1]['success'][0] and not any(r['terminated'][0] for r in log[:-1])
+    assert sum(r['reward'][0] for r in log) == pytest.approx(3.0 - 0.1 * len(log), abs=1e-9)

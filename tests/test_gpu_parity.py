@@ -684,6 +684,33 @@ def test_box_button_press_through_the_physics(precision):
     _record('box_button_press', dict(precision=precision, pressed_at_step=int(pressed_at), button=float(button.mean())))
 
 
+@pytest.mark.parametrize('precision', ['f64', 'f32'])
+def test_box_task_solved_by_the_scripted_policy_on_the_device(precision):
+    """The whole Box-v0 task through the physics on the device (tests/scripted_box.py: grasp the handle bar, lift the door along
+    its arc past 1.9 rad, let go, press the button, push the door shut): the three +1 transitions and the final terminated /
+    is_success happen on the device as on the oracle — on the same steps in fp64, within 2 steps in fp32 (free-running, ~17 k
+    ticks of contact dynamics per env)."""
+    import scripted_box as SB
+    n = 2
+    ob, gb = O.OracleBatch('Box', n, seed=1), _batch('Box', n, seed=1, precision=precision)
+    ob.reset(); gb.reset()
+    log_o = SB.run(lambda a: ob.step(a), n)
+
+    def dev_step(a):
+        gb.step(a, autoreset=False)
+        return dict(obs=_np(gb.obs).astype(np.float64), reward=_np(gb.reward).astype(np.float64), terminated=_np(gb.terminated).astype(bool),
+                    success=_np(gb.success).astype(bool))
+    log_g = SB.run(dev_step, n)
+    wo = [k for k, r in enumerate(log_o) if (r['reward'] > 0.5).all()]
+    wg = [k for k, r in enumerate(log_g) if (r['reward'] > 0.5).all()]
+    _record('box_scripted_task', dict(precision=precision, steps_oracle=len(log_o), steps_device=len(log_g), wins_oracle=wo, wins_device=wg))
+    assert len(wo) == 3 and len(wg) == 3, (wo, wg)
+    assert log_g[-1]['terminated'].all() and log_g[-1]['success'].all() and len(log_g) < 200
+    tol = 0 if precision == 'f64' else 2
+    assert all(abs(a - b) <= tol for a, b in zip(wo, wg)) and abs(len(log_o) - len(log_g)) <= tol, (wo, wg)
+    assert gb.stats()['capacity_overflow_ticks'] <= 0.01 * gb.stats()['ticks']
+
+
 def test_box_step_logic_matches_the_reference_fixture():
     """The device env logic of Box-v0 against the cases recorded from the reference's own BoxManipulation.step()
     (tests/golden/reference_box_logic.json): observation <= 2e-5, reward <= 2e-6, terminated / is_success / sticky bits exact,
