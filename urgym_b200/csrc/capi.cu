@@ -4,6 +4,7 @@
 #include <cstdio>
 #include <cstring>
 #include <cstdlib>
+#include <mutex>
 #include <string>
 #include <vector>
 
@@ -134,6 +135,8 @@ StaticScratch* g_static_ptr[16] = {nullptr};   // per device: the array's addres
 int static_setup(int device, StaticScratch** out) {
   if (device < 0 || device >= 16) return fail(URGYM_E_ARG, "urgym_step_static: device out of range");
   CK(cudaSetDevice(device));
+  static std::mutex mu;                       // two host threads may make their first call on a device at the same time
+  std::lock_guard<std::mutex> lock(mu);
   if (!g_static_ptr[device]) {
     StaticScratch* p = nullptr;
     CK(cudaGetSymbolAddress((void**)&p, g_static_scratch));
