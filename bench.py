@@ -11,7 +11,7 @@ goes through the C ABI's host-buffer entry (urgym_step_host: H2D of the actions,
 flags) and is timed with the host clock around the synchronous calls, over the same K steps.
 
 The headline (`value`, `e2e`, `roofline`) is BASELINE.json config 1 (BallBalance x 4096 on one GPU). The same line carries a
-`workloads` block with BASELINE configs 2-4 and Golf at 16 384 envs per GPU (value, ms per step, ticks per env-step, e2e),
+`workloads` block with BASELINE configs 2-4, Golf and Box at 16 384 envs per GPU (value, ms per step, ticks per env-step, e2e),
 measured right after the headline with fewer steps (--side-steps), so that the driver's BENCH / SCALE records hold every
 config at every GPU count; `--no-side` skips them.
 """
@@ -186,7 +186,7 @@ def cpu_arm(env, seconds, steps=None, warmup=0, envs_per_thread=4, seed=1234):
     return total / wall, cores, desc, (wall / nsteps * 1e3 if nsteps else None), total
 
 
-SIDE_WORKLOADS = ['two16384', 'push16384', 'grasp16384', 'golf16384']   # BASELINE configs 2-4 and Golf, 16 384 envs per GPU
+SIDE_WORKLOADS = ['two16384', 'push16384', 'grasp16384', 'golf16384', 'box16384']   # BASELINE configs 2-4, Golf and Box, 16 384 envs per GPU
 
 
 def measure(env, n_envs, K, W, rank, world, local, torch, dist, with_e2e=True, with_clocks=False, seed=20261104):

@@ -85,6 +85,22 @@ class OracleBatch:
         return dict(obs=obs, reward=rew, terminated=term.astype(bool), truncated=trunc.astype(bool),
                     success=succ.astype(bool), final_obs=fin, nticks=nt)
 
+    def step_parallel(self, action, u=None, draws=None, autoreset=False, threads=None):
+        """step() with the envs spread over host threads (envs are independent; ctypes releases the GIL): same results."""
+        from concurrent.futures import ThreadPoolExecutor
+        threads = min(threads or (os.cpu_count() or 1), self.n)
+        if threads <= 1:
+            return self.step(action, u=u, draws=draws, autoreset=autoreset)
+        cuts = np.linspace(0, self.n, threads + 1).astype(int)
+        with ThreadPoolExecutor(threads) as ex:
+            parts = list(ex.map(lambda i: self.step(action, u=u, draws=draws, autoreset=autoreset, lo=int(cuts[i]), hi=int(cuts[i + 1])), range(threads)))
+        out = parts[0]
+        for i in range(1, threads):
+            sl = slice(int(cuts[i]), int(cuts[i + 1]))
+            for k in out:
+                out[k][sl] = parts[i][k][sl]
+        return out
+
     def get_state(self):
         s = np.zeros((self.n, STATE_SLOTS)); self.L.urgo_get_state(self.h, _p(s)); return s
 
