@@ -752,6 +752,19 @@ def test_vector_env_and_single_env_api():
             break
     assert k == 49 and trunc or term
     e.close()
+    # Box-v0 through the reference's constructor signature (env_box_v0.py:21) and through the vector env
+    e = E.make('URGym/Box-v0', button_touch_mode='any', render_mode='train')
+    o, inf = e.reset()
+    assert o.shape == (7,) and o.dtype == np.float64 and abs(np.linalg.norm(o[3:]) - 1) < 1e-5 and e.action_space.shape == (8,)
+    o, r, term, trunc, inf = e.step(e.action_space.sample())
+    assert r == pytest.approx(-0.1, abs=1e-6) and not term and not trunc and inf == {'is_success': False}
+    e.close()
+    v = E.URGymVectorEnv('URGym/Box-v0', 64, seed=2)
+    obs, info = v.reset()
+    assert obs.shape == (64, 7) and (info['reset_ticks'] == 10).all()
+    obs, rew, term, trunc, info = v.step(torch.zeros(64, 8, device=obs.device))
+    assert (info['nticks'][:, 0] == 120).all() and not term.any() and v.max_episode_steps == 200
+    v.close()
 
 
 def test_sb3_vec_env_protocol():
