@@ -55,7 +55,7 @@ def test_static_queries_work_without_a_device(L):
         assert (L.urgym_obs_dim(t), L.urgym_act_dim(t), L.urgym_max_episode_steps(t)) == (od, ad, ms)
         g, sm = C.c_int(), C.c_int()
         assert L.urgym_kernel_info(t, C.byref(g), C.byref(sm)) == 0
-        assert g.value == 32 and 0 < sm.value <= (17, 17, 21, 17, 36, 21, 36, 21)[t] * 1024   # 13 (10 CubesPush / Box, 6 Golf scenes) resident envs per SM
+        assert g.value == 32 and 0 < sm.value <= (15.2, 15.2, 19.4, 15.2, 36, 19.4, 36, 19.6)[t] * 1024   # 14 (11 CubesPush / Box, 6 Golf scenes) resident envs per SM
     assert L.urgym_obs_dim(8) < 0
     assert L.urgym_real_bytes() == 4 and [L.urgym_num_pairs(t) for t in range(8)] == [73, 94, 73, 35, 134, 73, 134, 158]
 

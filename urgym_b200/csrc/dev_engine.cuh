@@ -17,12 +17,26 @@
 
 // Manifold point. Side A is a robot link (ra >= 0, pa = world point) or a free body (fa >= 0, pa = point relative
 // to the body origin); side B is a free body (fb >= 0, rb relative) or static. n points from B to A.
-struct Con {
+// Restitution and rolling friction are non-zero in the Golf scenes only (club 0.1 x ball 0.1; the ball's rollingFriction) and Box-v0
+// borrows `rest` for its motor row: the other scenes' records do without the two words (160 B per env: one more resident warp per SM).
+template <bool FULL> struct ConT;
+template <> struct ConT<true> {
   int shapes;   // sa | sb << 8
   int bodies;   // (fa + 1) | (fb + 1) << 8 | (ra + 1) << 16
   real pa[3], rb[3], n[3];
   real dist, mu, rest, roll;
 };
+template <> struct ConT<false> {
+  int shapes, bodies;
+  real pa[3], rb[3], n[3];
+  real dist, mu;
+};
+UG_DEV real con_rest(const ConT<true>& c) { return c.rest; }
+UG_DEV real con_rest(const ConT<false>&) { return 0._r; }
+UG_DEV real con_roll(const ConT<true>& c) { return c.roll; }
+UG_DEV real con_roll(const ConT<false>&) { return 0._r; }
+UG_DEV void con_set_rest_roll(ConT<true>& c, real rest, real roll) { c.rest = rest; c.roll = roll; }
+UG_DEV void con_set_rest_roll(ConT<false>&, real, real) {}
 
 template <int NCAP, int RC, bool ANCH = false>
 struct SmemT {
@@ -30,6 +44,8 @@ struct SmemT {
   // the scene has world-anchored 1-DoF bodies (Box-v0's door and button): every branch that serves them is compiled under this flag,
   // so the kernels of the other scenes carry none of it (same instructions, same bits as before Box-v0 existed)
   static constexpr bool ANCHORS = ANCH;
+  static constexpr bool FULLCON = ANCH || RC > 3 * NCAP;   // rolling-friction rows exist (Golf scenes) or Box-v0
+  typedef ConT<FULLCON> Con;
   static constexpr int TTRI = RC * (RC + 1) / 2;  // packed lower triangle of the symmetric contact block
   // ---- state that lives across the ticks of one gym step
   real q[UG_NDOF], qd[UG_NDOF], tgt[8];
@@ -42,9 +58,10 @@ struct SmemT {
   real fR[UG_MAXFREE][9], fIinv[UG_MAXFREE][6];
   Con con[NCAP];
   real lam[UG_JMAX + RC];
-  int jdesc[UG_JMAX];  // col | type << 8 | index << 12
-  int jci4[UG_JMAX + 2];  // byte offset of row j's column inside an E row, at [j + 1] (one slack entry on each side)
-  int cdesc[RC];       // contact | type << 8 | dir << 12
+  // row descriptors in 16 bits (240 B per env less than as ints; together with the shorter manifold records: 14 instead of 13 resident warps)
+  unsigned short jdesc[UG_JMAX];  // col | type << 8 | index << 12
+  unsigned short jci4[UG_JMAX + 2];  // byte offset of row j's column inside an E row, at [j + 1] (one slack entry on each side)
+  unsigned short cdesc[RC];       // contact | type << 8 | dir << 12
   // rows 0..16: extended M^-1 (17 x 17); rows 17..: robot velocity response of each contact row in the same 17 columns
   real E[(UG_NCOL + RC) * UG_NCOL];
   union alignas(16) {

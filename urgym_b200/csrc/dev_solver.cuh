@@ -90,10 +90,10 @@ __device__ __noinline__ void collide(S& s, const DevModel& M, const Gp<G> gp) {
         for (int k = 0; k < 3; k++) {
           real pen = k == 0 ? qa - M.flower[b] : (k == 1 ? M.fupper[b] - qa : qa);
           if (k < 2 ? pen > 0._r : !(M.fmotor[b] > 0._r)) continue;
-          Con& c = s.con[base++];
+          typename S::Con& c = s.con[base++];
           c.shapes = UG_PSEUDO | (k < 2 ? 1 : 2) | (an == 1 ? 4 : 0); c.bodies = b + 1;
           st3(c.pa, mk3(0, 0, 0)); st3(c.rb, mk3(0, 0, 0)); st3(c.n, k == 1 ? -ax : ax);
-          c.dist = pen; c.mu = 0._r; c.rest = M.fmotor[b]; c.roll = 0._r;
+          c.dist = pen; c.mu = 0._r; con_set_rest_roll(c, M.fmotor[b], 0._r);
         }
       }
     }
@@ -200,12 +200,12 @@ __device__ __noinline__ void collide(S& s, const DevModel& M, const Gp<G> gp) {
       for (int i = 0; i < n; i++) {
         int idx = base + excl + i;
         if (idx < NCAP) {
-          Con& c = s.con[idx];
+          typename S::Con& c = s.con[idx];
           c.shapes = sa | (sb << 8); c.bodies = (fa + 1) | ((fb + 1) << 8) | ((ra + 1) << 16);
           st3(c.pa, fa >= 0 ? pts[i].posA - ld3(s.fpos[fa]) : pts[i].posA);
           st3(c.rb, fb >= 0 ? pts[i].posB - ld3(s.fpos[fb]) : pts[i].posB);
           st3(c.n, pts[i].n);
-          c.dist = pts[i].dist; c.mu = mu; c.rest = A.rest * B.rest; c.roll = i == 0 ? roll : 0._r;
+          c.dist = pts[i].dist; c.mu = mu; con_set_rest_roll(c, A.rest * B.rest, i == 0 ? roll : 0._r);
         }
       }
     }
@@ -226,7 +226,7 @@ struct CRow {
 template <class S>
 UG_DEV void build_crow(const S& s, const DevModel& M, int desc, CRow& r, bool robot_part) {
   const int k = desc & 255, type = (desc >> 8) & 15, dir = desc >> 12;
-  const Con& c = s.con[k];
+  const typename S::Con& c = s.con[k];
   f3 n = ld3(c.n), t1, t2; plane_space(n, t1, t2);
   f3 dv = type == RT_NORMAL ? n : (dir == 0 ? t1 : t2);
   const bool lin = type != RT_ROLL && (!S::ANCHORS || (c.shapes & (UG_PSEUDO | 4)) != (UG_PSEUDO | 4));
@@ -312,16 +312,16 @@ __device__ __noinline__ real solve_and_integrate(S& s, const DevModel& M, const 
     }
     unsigned lm = gp.ballot(lim != 0);
     int nl = __popc(lm);
-    if (lim) { const int p_ = __popc(lm & ((1u << l) - 1u)); s.jdesc[p_] = l | ((lim == 1 ? RT_LIM_LO : RT_LIM_HI) << 8) | (l << 12); s.jci4[p_ + 1] = (int)UG_RB * l; }
+    if (lim) { const int p_ = __popc(lm & ((1u << l) - 1u)); s.jdesc[p_] = (unsigned short)(l | ((lim == 1 ? RT_LIM_LO : RT_LIM_HI) << 8) | (l << 12)); s.jci4[p_ + 1] = (unsigned short)(UG_RB * l); }
     int nm = 0;
     const int fl = s.flags;
-    if (fl & FL_ARM) { if (l < 6) { s.jdesc[nl + l] = l | (RT_MOTOR << 8) | (l << 12); s.jci4[nl + l + 1] = (int)UG_RB * l; } nm = 6; }
-    if (fl & FL_GRIP) { if (l == 0) { s.jdesc[nl + nm] = 6 | (RT_MOTOR << 8) | (6 << 12); s.jci4[nl + nm + 1] = (int)UG_RB * 6; } nm++; }
-    if (l < 5) { s.jdesc[nl + nm + l] = (12 + l) | (RT_GEAR << 8) | (l << 12); s.jci4[nl + nm + l + 1] = (int)UG_RB * (12 + l); }
+    if (fl & FL_ARM) { if (l < 6) { s.jdesc[nl + l] = (unsigned short)(l | (RT_MOTOR << 8) | (l << 12)); s.jci4[nl + l + 1] = (unsigned short)(UG_RB * l); } nm = 6; }
+    if (fl & FL_GRIP) { if (l == 0) { s.jdesc[nl + nm] = (unsigned short)(6 | (RT_MOTOR << 8) | (6 << 12)); s.jci4[nl + nm + 1] = (unsigned short)(UG_RB * 6); } nm++; }
+    if (l < 5) { s.jdesc[nl + nm + l] = (unsigned short)((12 + l) | (RT_GEAR << 8) | (l << 12)); s.jci4[nl + nm + l + 1] = (unsigned short)(UG_RB * (12 + l)); }
     n_nc = nl + nm + 5;
     if (l == 0) { s.jci4[0] = 0; s.jci4[n_nc + 1] = 0; }  // slack entries: the sweeps prefetch one row ahead
     if (l < NC) s.cdesc[l] = l | (RT_NORMAL << 8);
-    bool rl = l < NC && s.con[l].roll > 0._r;
+    bool rl = l < NC && con_roll(s.con[l]) > 0._r;
     unsigned rm = gp.ballot(rl);
     constexpr int NROLL = (RC - 3 * S::NC_CAP) / 2;  // rolling-friction manifolds a tick can carry (Golf scenes: 4, else 0)
     NT = 2 * min(__popc(rm), NROLL);
@@ -410,22 +410,22 @@ __device__ __noinline__ real solve_and_integrate(S& s, const DevModel& M, const 
         real inv = 1.0_r / dn;
         if (S::ANCHORS && !(dn > 1e-20_r)) inv = 0._r;   // a row no body can move along (a tangent across a hinge axis) stays inert
         p0.y = inv; p0.z = dn;
-        const Con& cn = s.con[k];
+        const typename S::Con& cn = s.con[k];
         if (S::ANCHORS && type == RT_NORMAL && (cn.shapes & UG_PSEUDO)) {
           if (cn.shapes & 1) {   // joint limit of an anchored body: the robot's limit row formula
             p0.x = (-cn.dist * UGP_ERP * UGP_INV_DT - rel) * inv; p0.w = 0._r; p1.x = UGP_LIMIT_MAX_IMPULSE;
           } else {               // position motor to coordinate 0 (cn.dist = coordinate, cn.rest = force limit)
             const real want = UGP_MOTOR_KP * (0._r - cn.dist) * UGP_INV_DT + (1.0_r - UGP_MOTOR_KD) * rel;
-            p0.x = (want - rel) * inv; p0.w = -cn.rest * UGP_DT; p1.x = cn.rest * UGP_DT;
+            p0.x = (want - rel) * inv; p0.w = -con_rest(cn) * UGP_DT; p1.x = con_rest(cn) * UGP_DT;
           }
         } else if (type == RT_NORMAL) {
           real pen = cn.dist + UGP_LINEAR_SLOP, rest = 0._r;
-          if (rabs(rel) >= UGP_RESTITUTION_VEL_THRESHOLD) rest = rmax(cn.rest * -rel, 0._r);
+          if (rabs(rel) >= UGP_RESTITUTION_VEL_THRESHOLD) rest = rmax(con_rest(cn) * -rel, 0._r);
           real pos_e = 0._r, vel_e = rest - rel;
           if (pen > 0._r) vel_e -= pen * UGP_INV_DT; else pos_e = -pen * UGP_ERP2 * UGP_INV_DT;
           p0.x = (pos_e + vel_e) * inv; p0.w = 0._r; p1.x = 1e10_r;
         } else {
-          p0.x = -rel * inv; p1.x = type == RT_ROLL ? cn.roll : cn.mu; p1.y = (real)k;
+          p0.x = -rel * inv; p1.x = type == RT_ROLL ? con_roll(cn) : cn.mu; p1.y = (real)k;
         }
       } else {
 #pragma unroll
@@ -473,7 +473,7 @@ __device__ __noinline__ real solve_and_integrate(S& s, const DevModel& M, const 
       const int dp = s.cdesc[cp], tp = (dp >> 8) & 15;
       real acc = 0._r;
       if (tp != RT_PAD) {
-        const Con& cn = s.con[dp & 255];
+        const typename S::Con& cn = s.con[dp & 255];
         f3 n = ld3(cn.n), t1, t2; plane_space(n, t1, t2);
         f3 dv = tp == RT_NORMAL ? n : ((dp >> 12) == 0 ? t1 : t2);
         const bool angrow = tp == RT_ROLL || (S::ANCHORS && (cn.shapes & (UG_PSEUDO | 4)) == (UG_PSEUDO | 4));

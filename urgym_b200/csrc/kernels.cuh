@@ -74,13 +74,13 @@ template <int ENVF> struct EnvNC { static constexpr int value = Scene<ENVF>::val
 template <int ENVF> struct EnvRC { static constexpr int value = 3 * EnvNC<ENVF>::value + (Scene<ENVF>::value == 4 ? 8 : 0); };
 template <int ENVF> using EnvSmem = SmemT<EnvNC<ENVF>::value, EnvRC<ENVF>::value, Scene<ENVF>::value == 7>;
 
-// Resident CTAs per SM asked of ptxas. The CubesPush / Box kernels (20.2 KB per env: 10 CTAs fit) may use 164 registers instead of
-// 128 (+2.9 % CubesPush, Box unchanged). The Golf kernels keep the 128-register cap although only 6 CTAs fit their 34.5 KB: with 240
+// Resident CTAs per SM asked of ptxas = what the scene's shared memory allows: 14 at 15.5 KB per env (ball scenes, CubesGrasp), 11 at
+// 19.8 KB (CubesPush, Box: they may use up to 186 registers instead of 128; +2.9 % CubesPush when first allowed 164). The Golf kernels keep the 128-register cap although only 6 CTAs fit their 34.5 KB: with 240
 // registers and no spills they measured 2-5 % SLOWER (profiles/r02_ab_running_pointers.txt), so the cap stays.
 #ifdef UG_F64
 template <int ENVF> struct EnvMinCtas { static constexpr int value = UG_MIN_CTAS; };
 #else
-template <int ENVF> struct EnvMinCtas { static constexpr int value = (EnvRC<ENVF>::value > 60 && EnvRC<ENVF>::value <= 100) ? 10 : UG_MIN_CTAS; };
+template <int ENVF> struct EnvMinCtas { static constexpr int value = EnvRC<ENVF>::value <= 60 ? 14 : (EnvRC<ENVF>::value <= 100 ? 11 : UG_MIN_CTAS); };
 #endif
 template <int ENVF, int G>
 __global__ void __launch_bounds__(32, EnvMinCtas<ENVF>::value) env_kernel(KParams P) {
