@@ -270,3 +270,25 @@ def test_scripted_grasp_reaches_every_sub_goal_through_the_physics():
     last = log[-1][1]
     assert last['terminated'].all() and last['success'].all() and np.allclose(last['reward'], 9.9) and (last['obs'][:, 12] > 0.2).all()
     assert len(log) <= 20                                          # inside the env's 20-step TimeLimit
+
+
+def test_recorded_episode_statistics_are_of_this_oracle():
+    """tests/golden/episode_stats_oracle.json (the oracle's side of the GPU suite's 1e4-episode test, recorded by
+    tests/golden/make_episode_stats.py) must be regenerated when oracle/ changes: a small fresh sample of the same policy has to
+    land on the recorded means (CubesPush: every episode runs its 50 steps; return -5.19 with a per-episode spread of 0.09)."""
+    want = json.load(open(os.path.join(ROOT, 'tests', 'golden', 'episode_stats_oracle.json')))['CubesPush']
+    n = 48
+    ob = O.OracleBatch('CubesPush', n, seed=41)
+    ob.reset()
+    rng = np.random.default_rng(11)
+    ret, eps = np.zeros(n), []
+    for k in range(50):
+        a = rng.uniform(-0.1, 0.1, (n, 3)).astype(np.float32).astype(np.float64); rng.uniform(0, 1, n)
+        r = ob.step_parallel(a, autoreset=True)
+        ret += r['reward']
+        done = r['terminated'] | r['truncated']
+        eps += ret[done].tolist(); ret[done] = 0
+    assert len(eps) == n
+    se = np.sqrt(want['var']['return'] / n)
+    assert abs(np.mean(eps) - want['mean']['return']) < 5 * se + 0.01, (np.mean(eps), want['mean'])
+    assert want['mean']['length'] == 50.0 and want['episodes'] >= 10000
